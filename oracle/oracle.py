@@ -1,0 +1,194 @@
+"""ctypes binding of the CPU oracle (oracle/gp_oracle.c).
+
+TEST INFRASTRUCTURE ONLY -- see the header of gp_oracle.c.  Imported by tests/, by
+__graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference legs, never by the
+product package.  Parity unpinned (the reference ships no golden vectors for this path).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libgp_oracle.so")
+
+SE, WHITE = 0, 1
+
+
+class Term(C.Structure):
+    _fields_ = [("kind", C.c_int), ("p0", C.c_double), ("p1", C.c_double), ("p2", C.c_double)]
+
+
+class LL(C.Structure):
+    _fields_ = [("Q", C.c_double), ("U1", C.c_double), ("S", C.c_double), ("ll_ref", C.c_double),
+                ("ll_gpml", C.c_double), ("n", C.c_int), ("info", C.c_int)]
+
+
+def build():
+    src = os.path.join(_HERE, "gp_oracle.c")
+    if not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        L.orc_cov_fn.restype = C.c_double
+        L.orc_cov_fn.argtypes = [C.POINTER(Term), C.c_int, C.c_double]
+        L.orc_prior.restype = C.c_double
+        L.orc_invgamma_logpdf.restype = C.c_double
+        L.orc_invgamma_logpdf.argtypes = [C.c_double] * 3
+        _lib = L
+    return _lib
+
+
+def terms_array(terms):
+    """terms: list of ("se", h, sigma) | ("white", sigma)"""
+    arr = (Term * len(terms))()
+    for i, t in enumerate(terms):
+        if t[0] == "se":
+            arr[i] = Term(SE, float(t[1]), float(t[2]), 0.0)
+        elif t[0] == "white":
+            arr[i] = Term(WHITE, float(t[1]), 0.0, 0.0)
+        else:
+            raise ValueError(t[0])
+    return arr
+
+
+def _d(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a, a.ctypes.data_as(_dp)
+
+
+def _xsoa(x):
+    """x: (n,) or (n, dim) -> SoA [dim][n] contiguous, dim"""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    return np.ascontiguousarray(x.T), x.shape[1]
+
+
+def cov_fn(terms, d):
+    return lib().orc_cov_fn(terms_array(terms), len(terms), float(d))
+
+
+def build_cov(x, terms, nugget):
+    xs, dim = _xsoa(x)
+    n = xs.shape[1]
+    K = np.empty((n, n), dtype=np.float64)
+    lib().orc_build_cov(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), terms_array(terms),
+                        C.c_int(len(terms)), C.c_double(nugget), K.ctypes.data_as(_dp))
+    return K.T  # column-major buffer viewed as (row, col)
+
+
+def potrf_lower(K):
+    """K (n,n) symmetric -> (L lower with zero upper, info)"""
+    n = K.shape[0]
+    a = np.array(K.T, dtype=np.float64, order="C")  # buffer = column-major of K
+    info = lib().orc_potrf_lower(C.c_int(n), a.ctypes.data_as(_dp), C.c_int(n))
+    lib().orc_zero_upper(C.c_int(n), a.ctypes.data_as(_dp), C.c_int(n))
+    return a.T.copy(), info
+
+
+def trsv_lower(L, b):
+    n = L.shape[0]
+    a = np.array(L.T, dtype=np.float64, order="C")
+    xv = np.array(b, dtype=np.float64)
+    lib().orc_trsv_lower(C.c_int(n), a.ctypes.data_as(_dp), C.c_int(n), xv.ctypes.data_as(_dp))
+    return xv
+
+
+def trsv_upper(U, b):
+    n = U.shape[0]
+    a = np.array(U.T, dtype=np.float64, order="C")
+    xv = np.array(b, dtype=np.float64)
+    lib().orc_trsv_upper(C.c_int(n), a.ctypes.data_as(_dp), C.c_int(n), xv.ctypes.data_as(_dp))
+    return xv
+
+
+def trsm_upper(U, B):
+    m, nrhs = B.shape
+    a = np.array(U.T, dtype=np.float64, order="C")
+    bb = np.array(B.T, dtype=np.float64, order="C")
+    lib().orc_trsm_upper(C.c_int(m), C.c_int(nrhs), a.ctypes.data_as(_dp), C.c_int(m),
+                         bb.ctypes.data_as(_dp), C.c_int(m))
+    return bb.T.copy()
+
+
+def loglik(x, y, terms, beta=(), nugget=1e-3, long_double=False):
+    xs, dim = _xsoa(x)
+    n = xs.shape[1]
+    yv, yp = _d(y)
+    bv, bp = _d(np.asarray(beta, dtype=np.float64) if len(beta) else np.zeros(1))
+    out = LL()
+    if long_double:
+        rc = lib().orc_loglik_ld(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp,
+                                 terms_array(terms), C.c_int(len(terms)), bp, C.c_int(len(beta)),
+                                 C.c_double(nugget), C.byref(out))
+    else:
+        work = np.empty(n * n + n, dtype=np.float64)
+        rc = lib().orc_loglik(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp,
+                              terms_array(terms), C.c_int(len(terms)), bp, C.c_int(len(beta)),
+                              C.c_double(nugget), work.ctypes.data_as(_dp), C.byref(out))
+    assert rc == 0
+    return {k: getattr(out, k) for k, _ in LL._fields_}
+
+
+def predict(x, y, terms, xstar, nugget=1e-6):
+    xs, dim = _xsoa(x)
+    n = xs.shape[1]
+    xt, dim2 = _xsoa(xstar)
+    assert dim == dim2
+    m = xt.shape[1]
+    yv, yp = _d(y)
+    mean = np.empty(m)
+    var = np.empty(m)
+    work = np.empty(n * n + 2 * n, dtype=np.float64)
+    info = C.c_int(0)
+    lib().orc_predict(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp, terms_array(terms),
+                      C.c_int(len(terms)), C.c_double(nugget), C.c_int(m), xt.ctypes.data_as(_dp),
+                      mean.ctypes.data_as(_dp), var.ctypes.data_as(_dp), work.ctypes.data_as(_dp),
+                      C.byref(info))
+    return mean, var, info.value
+
+
+def nparams(terms):
+    return sum(2 if t[0] == "se" else 1 for t in terms)
+
+
+def prior(terms, ig):
+    igv, igp = _d(ig)
+    return lib().orc_prior(terms_array(terms), C.c_int(len(terms)), igp)
+
+
+def mh_run(x, y, init_terms, ig, delta, z, u, beta=(), nugget=1e-3, formula=0, evals_per_iter=1):
+    """z: (iters, P) standard normals; u: (iters,) uniforms; ig: (P, 2) inverse-gamma (shape, scale)."""
+    xs, dim = _xsoa(x)
+    n = xs.shape[1]
+    yv, yp = _d(y)
+    P = nparams(init_terms)
+    zv, zp = _d(z)
+    uv, up = _d(u)
+    iters = uv.shape[0]
+    assert zv.shape == (iters, P)
+    igv, igp = _d(ig)
+    assert igv.shape == (P, 2)
+    bv, bp = _d(np.asarray(beta, dtype=np.float64) if len(beta) else np.zeros(1))
+    states = np.empty((iters, P))
+    ll = np.empty(iters)
+    acc = np.empty(iters, dtype=np.int32)
+    rc = lib().orc_mh_run(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp,
+                          terms_array(init_terms), C.c_int(len(init_terms)), bp,
+                          C.c_int(len(beta)), C.c_double(nugget), igp, C.c_double(delta),
+                          C.c_int(iters), zp, up, C.c_int(formula), C.c_int(evals_per_iter),
+                          states.ctypes.data_as(_dp), ll.ctypes.data_as(_dp),
+                          acc.ctypes.data_as(_ip))
+    return states, ll, acc, rc

@@ -1,0 +1,378 @@
+// gpb_api.cu -- the C ABI of libgpb200.so (include/gpb200.h): contexts, datasets, workspace and
+// the host-side sequencing of the sm_100a kernels.  No CPU fallback anywhere: every entry point
+// either runs the CUDA path or returns an error status.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "gpb_internal.h"
+
+using namespace gpb;
+
+struct gpb_ctx {
+  int device = 0;
+  int num_sms = 0;
+  int sched_mode = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  // workspace (grown on demand, never shrunk)
+  double* mats = nullptr;   size_t mats_doubles = 0;
+  double* linvt = nullptr;  size_t linvt_doubles = 0;
+  int* done = nullptr;      size_t done_ints = 0;
+  int* info = nullptr;      size_t info_ints = 0;
+  Hyper* hyper = nullptr;   size_t hyper_n = 0;
+  gpb_ll* ll = nullptr;     size_t ll_n = 0;
+  double* aux = nullptr;    size_t aux_doubles = 0;   // xstar / predictive outputs / MH state
+  SchedState* sched = nullptr;
+  SchedState* h_sched = nullptr;  // pinned
+  // pinned host staging
+  Hyper* h_hyper = nullptr; size_t h_hyper_n = 0;
+  gpb_ll* h_ll = nullptr;   size_t h_ll_n = 0;
+  long long launches = 0;
+  float timing[3] = {0, 0, 0};
+  std::string cuda_err;
+};
+
+struct gpb_dataset {
+  gpb_ctx* ctx;
+  int n, dim;
+  double* x;  // SoA [dim][n]
+  double* y;  // [n]
+};
+
+namespace {
+
+int cuda_fail(gpb_ctx* ctx, cudaError_t e, const char* where) {
+  if (ctx) ctx->cuda_err = std::string(where) + ": " + cudaGetErrorString(e);
+  return (e == cudaErrorMemoryAllocation) ? GPB_E_NOMEM : GPB_E_CUDA;
+}
+#define CK(call)                                             \
+  do {                                                       \
+    cudaError_t e_ = (call);                                 \
+    if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); \
+  } while (0)
+
+template <typename T>
+int grow(gpb_ctx* ctx, T** p, size_t* have, size_t want) {
+  if (*have >= want) return GPB_OK;
+  if (*p) { cudaFree(*p); *p = nullptr; *have = 0; }
+  cudaError_t e = cudaMalloc((void**)p, want * sizeof(T));
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(ctx, e, "cudaMalloc(workspace)"); }
+  *have = want;
+  return GPB_OK;
+}
+template <typename T>
+int grow_pinned(gpb_ctx* ctx, T** p, size_t* have, size_t want) {
+  if (*have >= want) return GPB_OK;
+  if (*p) { cudaFreeHost(*p); *p = nullptr; *have = 0; }
+  cudaError_t e = cudaMallocHost((void**)p, want * sizeof(T));
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(ctx, e, "cudaMallocHost"); }
+  *have = want;
+  return GPB_OK;
+}
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// m test points + (with_rhs ? 1 : 0) rhs row appended below the npad x npad square
+Geom make_geom(int n, int dim, int m, bool with_rhs, int batch) {
+  Geom g;
+  g.n = n; g.dim = dim; g.m = m;
+  g.npad = round_up(n, TILE);
+  g.apad = round_up(m + (with_rhs ? 1 : 0), TILE);
+  g.ld = g.npad + g.apad;
+  g.nt = g.npad / TILE;
+  g.rt = g.ld / TILE;
+  g.rhs_row = with_rhs ? g.npad + m : -1;
+  g.batch = batch;
+  g.mat_stride = (size_t)g.ld * g.npad;
+  return g;
+}
+
+int ensure_workspace(gpb_ctx* ctx, const Geom& g) {
+  int rc;
+  if ((rc = grow(ctx, &ctx->mats, &ctx->mats_doubles, g.mat_stride * g.batch))) return rc;
+  if ((rc = grow(ctx, &ctx->linvt, &ctx->linvt_doubles, (size_t)g.batch * g.nt * TILE * TILE))) return rc;
+  if ((rc = grow(ctx, &ctx->done, &ctx->done_ints, (size_t)g.batch * g.rt))) return rc;
+  if ((rc = grow(ctx, &ctx->info, &ctx->info_ints, (size_t)g.batch))) return rc;
+  if ((rc = grow(ctx, &ctx->hyper, &ctx->hyper_n, (size_t)g.batch))) return rc;
+  if ((rc = grow(ctx, &ctx->ll, &ctx->ll_n, (size_t)g.batch))) return rc;
+  if ((rc = grow_pinned(ctx, &ctx->h_hyper, &ctx->h_hyper_n, (size_t)g.batch))) return rc;
+  if ((rc = grow_pinned(ctx, &ctx->h_ll, &ctx->h_ll_n, (size_t)g.batch))) return rc;
+  return GPB_OK;
+}
+
+int fill_hyper(Hyper* h, const gpb_term* terms, int nterms, const double* beta, int nbeta, int dim) {
+  if (nterms < 1 || nterms > GPB_MAX_TERMS || !terms) return GPB_E_INVALID;
+  if (!(nbeta == 0 || nbeta == dim + 1)) return GPB_E_INVALID;
+  if (nbeta > 0 && !beta) return GPB_E_INVALID;
+  std::memset(h, 0, sizeof(Hyper));
+  h->nterms = nterms;
+  h->nbeta = nbeta;
+  for (int t = 0; t < nterms; ++t) {
+    if (terms[t].kind == GPB_KIND_MATERN) return GPB_E_UNSUPPORTED;
+    if (terms[t].kind != GPB_KIND_SE && terms[t].kind != GPB_KIND_WHITE) return GPB_E_INVALID;
+    h->kind[t] = terms[t].kind;
+    h->p0[t] = terms[t].p0;
+    h->p1[t] = terms[t].p1;
+  }
+  for (int i = 0; i < nbeta; ++i) h->beta[i] = beta[i];
+  return GPB_OK;
+}
+
+// build -> factor/solve on ctx->stream, with phase events
+int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y,
+               const double* d_xstar, double nugget) {
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+  launch_build(ctx->stream, g, d_x, d_y, d_xstar, ctx->hyper, nugget, ctx->mats, 0, 0);
+  ctx->launches += 1;
+  CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  ctx->launches += launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info,
+                               ctx->sched, ctx->sched_mode, ctx->num_sms);
+  CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+  return GPB_OK;
+}
+
+int finish_timing(gpb_ctx* ctx) {
+  CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_sched, ctx->sched, sizeof(SchedState), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&ctx->timing[i], ctx->ev[i], ctx->ev[i + 1]);
+  const SchedState s = *ctx->h_sched;
+  if (s.error != 0) {
+    ctx->cuda_err = "scheduler watchdog code " + std::to_string(s.error);
+    return GPB_E_WATCHDOG;
+  }
+  return GPB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gpb_version(void) { return "gpb200 0.1 (sm_100a)"; }
+
+const char* gpb_strerror(int status) {
+  switch (status) {
+    case GPB_OK: return "ok";
+    case GPB_E_INVALID: return "invalid argument";
+    case GPB_E_NODEVICE: return "no usable CUDA device (sm_100 required; there is no CPU fallback)";
+    case GPB_E_CUDA: return "CUDA runtime error";
+    case GPB_E_NOMEM: return "out of memory";
+    case GPB_E_UNSUPPORTED: return "unsupported (Matern kernel / dim > 2 are out of scope)";
+    case GPB_E_WATCHDOG: return "scheduler watchdog fired";
+    case GPB_E_NOTPD: return "covariance matrix not positive definite";
+    default: return "unknown status";
+  }
+}
+
+const char* gpb_last_cuda_error(const gpb_ctx* ctx) { return ctx ? ctx->cuda_err.c_str() : ""; }
+long long gpb_launch_count(const gpb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int gpb_last_timing(const gpb_ctx* ctx, float* t3) {
+  if (!ctx || !t3) return GPB_E_INVALID;
+  for (int i = 0; i < 3; ++i) t3[i] = ctx->timing[i];
+  return GPB_OK;
+}
+int gpb_set_sched(gpb_ctx* ctx, int mode) {
+  if (!ctx || mode < 0 || mode > 1) return GPB_E_INVALID;
+  ctx->sched_mode = mode;
+  return GPB_OK;
+}
+
+int gpb_ctx_create(int device, gpb_ctx** out) {
+  if (!out) return GPB_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return GPB_E_NODEVICE; }
+  if (device < 0 || device >= ndev) return GPB_E_INVALID;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return GPB_E_NODEVICE;
+  if (prop.major != 10) return GPB_E_NODEVICE;  // kernels are compiled for sm_100a only
+  gpb_ctx* ctx = new (std::nothrow) gpb_ctx();
+  if (!ctx) return GPB_E_NOMEM;
+  ctx->device = device;
+  ctx->num_sms = prop.multiProcessorCount;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&ctx->ev[i]);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->sched, sizeof(SchedState));
+  if (e == cudaSuccess) e = cudaMemset(ctx->sched, 0, sizeof(SchedState));
+  if (e == cudaSuccess) e = cudaMallocHost((void**)&ctx->h_sched, sizeof(SchedState));
+  if (e != cudaSuccess) { gpb_ctx_destroy(ctx); return GPB_E_CUDA; }
+  *out = ctx;
+  return GPB_OK;
+}
+
+void gpb_ctx_destroy(gpb_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  cudaFree(ctx->mats); cudaFree(ctx->linvt); cudaFree(ctx->done); cudaFree(ctx->info);
+  cudaFree(ctx->hyper); cudaFree(ctx->ll); cudaFree(ctx->aux); cudaFree(ctx->sched);
+  cudaFreeHost(ctx->h_hyper); cudaFreeHost(ctx->h_ll); cudaFreeHost(ctx->h_sched);
+  for (int i = 0; i < 4; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int gpb_dataset_create(gpb_ctx* ctx, int n, int dim, const double* x, const double* y,
+                       gpb_dataset** out) {
+  if (!ctx || !out || !x || n < 1) return GPB_E_INVALID;
+  if (dim != 1 && dim != 2) return GPB_E_UNSUPPORTED;
+  *out = nullptr;
+  CK(cudaSetDevice(ctx->device));
+  gpb_dataset* ds = new (std::nothrow) gpb_dataset();
+  if (!ds) return GPB_E_NOMEM;
+  ds->ctx = ctx; ds->n = n; ds->dim = dim; ds->x = nullptr; ds->y = nullptr;
+  cudaError_t e = cudaMalloc((void**)&ds->x, sizeof(double) * (size_t)n * dim);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ds->y, sizeof(double) * (size_t)n);
+  if (e == cudaSuccess) e = cudaMemcpy(ds->x, x, sizeof(double) * (size_t)n * dim, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    if (y) e = cudaMemcpy(ds->y, y, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice);
+    else e = cudaMemset(ds->y, 0, sizeof(double) * (size_t)n);
+  }
+  if (e != cudaSuccess) { gpb_dataset_destroy(ds); return cuda_fail(ctx, e, "gpb_dataset_create"); }
+  *out = ds;
+  return GPB_OK;
+}
+
+void gpb_dataset_destroy(gpb_dataset* ds) {
+  if (!ds) return;
+  cudaFree(ds->x); cudaFree(ds->y);
+  delete ds;
+}
+
+double gpb_ll_value(const gpb_ll* r, int formula) {
+  if (!r || r->info != 0) return NAN;
+  const double C = r->n * 0.5 * std::log(2 * M_PI);  // GaussianProcess.scala:126
+  if (formula == GPB_FORMULA_GPML) return -0.5 * r->Q - r->S - C;
+  return -0.5 * r->Q + 0.5 * (r->S + C) * r->U1;     // as parsed, SURVEY.md 0.1
+}
+
+int gpb_loglik_batch(gpb_ctx* ctx, const gpb_dataset* ds, int batch, const gpb_term* terms,
+                     int nterms, const double* beta, int nbeta, double nugget, gpb_ll* out) {
+  if (!ctx || !ds || ds->ctx != ctx || batch < 1 || !out) return GPB_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  const Geom g = make_geom(ds->n, ds->dim, 0, true, batch);
+  int rc = ensure_workspace(ctx, g);
+  if (rc) return rc;
+  for (int b = 0; b < batch; ++b) {
+    rc = fill_hyper(&ctx->h_hyper[b], terms + (size_t)b * nterms, nterms,
+                    nbeta ? beta + (size_t)b * nbeta : nullptr, nbeta, ds->dim);
+    if (rc) return rc;
+  }
+  CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper) * batch, cudaMemcpyHostToDevice, ctx->stream));
+  rc = run_system(ctx, g, ds->x, ds->y, nullptr, nugget);
+  if (rc) return rc;
+  launch_ll_epilogue(ctx->stream, g, ctx->mats, ctx->info, ctx->ll);
+  ctx->launches += 1;
+  CK(cudaMemcpyAsync(ctx->h_ll, ctx->ll, sizeof(gpb_ll) * batch, cudaMemcpyDeviceToHost, ctx->stream));
+  rc = finish_timing(ctx);
+  if (rc) return rc;
+  std::memcpy(out, ctx->h_ll, sizeof(gpb_ll) * batch);
+  return GPB_OK;
+}
+
+int gpb_loglik(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, int nterms,
+               const double* beta, int nbeta, double nugget, gpb_ll* out) {
+  return gpb_loglik_batch(ctx, ds, 1, terms, nterms, beta, nbeta, nugget, out);
+}
+
+int gpb_predict(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, int nterms,
+                double nugget, int m, const double* xstar, double* mean, double* var, int* info) {
+  if (!ctx || !ds || ds->ctx != ctx || m < 1 || !xstar || !mean || !var) return GPB_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  const Geom g = make_geom(ds->n, ds->dim, m, true, 1);
+  int rc = ensure_workspace(ctx, g);
+  if (rc) return rc;
+  // Predict.scala:80 uses the raw y: no mean function here (nbeta = 0)
+  rc = fill_hyper(&ctx->h_hyper[0], terms, nterms, nullptr, 0, ds->dim);
+  if (rc) return rc;
+  const size_t nx = (size_t)m * ds->dim;
+  if ((rc = grow(ctx, &ctx->aux, &ctx->aux_doubles, nx + 2 * (size_t)m))) return rc;
+  double* d_xstar = ctx->aux;
+  double* d_mean = ctx->aux + nx;
+  double* d_var = d_mean + m;
+  CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d_xstar, xstar, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
+  rc = run_system(ctx, g, ds->x, ds->y, d_xstar, nugget);
+  if (rc) return rc;
+  launch_pred_epilogue(ctx->stream, g, ctx->mats, ctx->hyper, d_mean, d_var);
+  ctx->launches += 1;
+  CK(cudaMemcpyAsync(mean, d_mean, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(var, d_var, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
+  int h_info = 0;
+  CK(cudaMemcpyAsync(&h_info, ctx->info, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  rc = finish_timing(ctx);
+  if (rc) return rc;
+  if (info) *info = h_info;
+  return GPB_OK;
+}
+
+
+static int build_to_host(gpb_ctx* ctx, int n, int dim, const double* x, const gpb_term* terms,
+                         int nterms, double nugget, double* out, int mode) {
+  if (!ctx || !x || !out || n < 1) return GPB_E_INVALID;
+  if (dim != 1 && dim != 2) return GPB_E_UNSUPPORTED;
+  CK(cudaSetDevice(ctx->device));
+  const Geom g = make_geom(n, dim, 0, false, 1);
+  int rc = ensure_workspace(ctx, g);
+  if (rc) return rc;
+  if (mode == 0) {
+    rc = fill_hyper(&ctx->h_hyper[0], terms, nterms, nullptr, 0, dim);
+    if (rc) return rc;
+  } else {
+    std::memset(&ctx->h_hyper[0], 0, sizeof(Hyper));
+  }
+  if ((rc = grow(ctx, &ctx->aux, &ctx->aux_doubles, (size_t)n * dim))) return rc;
+  CK(cudaMemcpyAsync(ctx->aux, x, sizeof(double) * (size_t)n * dim, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper), cudaMemcpyHostToDevice, ctx->stream));
+  launch_build(ctx->stream, g, ctx->aux, nullptr, nullptr, ctx->hyper, nugget, ctx->mats, mode, 1);
+  ctx->launches += 1;
+  CK(cudaMemcpy2DAsync(out, sizeof(double) * n, ctx->mats, sizeof(double) * g.ld, sizeof(double) * n,
+                       n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return GPB_OK;
+}
+
+int gpb_distance_matrix(gpb_ctx* ctx, int n, int dim, const double* x, double* D) {
+  return build_to_host(ctx, n, dim, x, nullptr, 0, 0.0, D, 1);
+}
+
+int gpb_build_cov(gpb_ctx* ctx, int n, int dim, const double* x, const gpb_term* terms, int nterms,
+                  double nugget, double* K) {
+  return build_to_host(ctx, n, dim, x, terms, nterms, nugget, K, 0);
+}
+
+int gpb_potrf(gpb_ctx* ctx, int n, double* A, int* info) {
+  if (!ctx || !A || n < 1) return GPB_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  const Geom g = make_geom(n, 1, 0, false, 1);
+  int rc = ensure_workspace(ctx, g);
+  if (rc) return rc;
+  CK(cudaMemsetAsync(ctx->mats, 0, sizeof(double) * g.mat_stride, ctx->stream));
+  CK(cudaMemcpy2DAsync(ctx->mats, sizeof(double) * g.ld, A, sizeof(double) * n, sizeof(double) * n, n,
+                       cudaMemcpyHostToDevice, ctx->stream));
+  launch_pad_identity(ctx->stream, g, ctx->mats);
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+  CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  ctx->launches += 1 + launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info,
+                                   ctx->sched, ctx->sched_mode, ctx->num_sms);
+  CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+  launch_zero_upper(ctx->stream, g, ctx->mats);
+  ctx->launches += 1;
+  CK(cudaMemcpy2DAsync(A, sizeof(double) * n, ctx->mats, sizeof(double) * g.ld, sizeof(double) * n, n,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+  int h_info = 0;
+  CK(cudaMemcpyAsync(&h_info, ctx->info, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  rc = finish_timing(ctx);
+  if (rc) return rc;
+  if (info) *info = h_info;
+  return GPB_OK;
+}
+
+}  // extern "C"

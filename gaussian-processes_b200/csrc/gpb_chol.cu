@@ -1,0 +1,347 @@
+// gpb_chol.cu -- k_chol_tasks: blocked FP64 Cholesky + the forward panel solves of the appended
+// rows (rhs and K*), as ONE persistent kernel that walks a left-looking tile task graph.
+//
+// Replaces (reference file:line under core/src/main/scala/gp/):
+//   breeze.linalg.cholesky -> F2J dpotrf("L")   call sites GaussianProcess.scala:123, Predict.scala:69
+//   Predict.forwardSolve   -> F2J dtrsv("L")    Predict.scala:40-45 (called at GaussianProcess.scala:124,
+//                                               Predict.scala:89-90): the rhs / K* rows are appended
+//                                               below K as extra tile rows, so  u^T = y^T L^-T  and
+//                                               V = K* L^-T fall out of the same panel solves.
+//
+// Task (b, i, j) = 64x64 tile (tile row i, tile column j) of proposal b:
+//     acc  = A_ij - sum_{k<j} L_ik L_jk^T          FP64 tensor cores (DMMA.8x8x4), operands streamed
+//                                                   by 1-D bulk async copies (TMA) through a 4-stage
+//                                                   mbarrier ring filled by a dedicated producer warp
+//     i==j : L_jj = chol(acc), and L_jj^-T by factoring the stacked [acc; I] (one row per thread in
+//            registers, one barrier per column)
+//     i>j  : L_ij = acc * L_jj^-T                   DMMA again
+// Tickets are handed out in topological order (by block column; diagonal first), dependencies are
+// per-tile-row progress counters polled with ld.acquire; every wait is bounded by a watchdog.
+// Summation order is fixed by the task, not by the schedule: results are bit-reproducible.
+//
+// Roofline: trailing contraction n^3/3 flop on the FP64 tensor pipe (37.1 TFLOP/s measured DMMA
+// issue peak on this B200, profiles/r01_dmma_shapes_microbench.log).
+#include "gpb_internal.h"
+
+namespace gpb {
+
+constexpr int KC = 16;                 // panel columns per pipeline stage
+constexpr int STAGES = 4;
+constexpr int NCONS = 128;             // consumer threads: 4 warps, 32x32 sub-tile each
+constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
+constexpr int STAGE_DOUBLES = 2 * KC * LDT;
+constexpr uint32_t STAGE_TX_BYTES = 2 * KC * TILE * sizeof(double);
+constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
+
+struct __align__(16) CholSmem {
+  double stage[STAGES][STAGE_DOUBLES];  // [0..KC) panel j ("c" rows), [KC..2KC) panel i ("r" rows)
+  double Cs[TILE * LDT];                // C tile, column-major [c][r]
+  double Ls[TILE * LDT];                // L_jj^-T tile, column-major [c][k]
+  double colbuf[2][2 * TILE];
+  uint64_t full[STAGES], empty[STAGES];
+  uint64_t tq_full[2], tq_empty[2];
+  int taskq[2];
+  int bad_col;
+};
+
+size_t chol_smem_bytes() { return sizeof(CholSmem); }
+
+struct TaskDesc { int b, i, j; };
+
+// tasks before block column j:  batch * sum_{j'<j} (rt - j')
+__device__ __forceinline__ long long col_start(const Geom& g, int j) {
+  return (long long)g.batch * ((long long)j * g.rt - (long long)j * (j - 1) / 2);
+}
+__device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcache) {
+  while (jcache + 1 < g.nt && (long long)t >= col_start(g, jcache + 1)) ++jcache;
+  while (jcache > 0 && (long long)t < col_start(g, jcache)) --jcache;
+  TaskDesc d;
+  d.j = jcache;
+  int local = t - (int)col_start(g, jcache);
+  if (local < g.batch) {
+    d.b = local; d.i = d.j;
+  } else {
+    int l2 = local - g.batch, per = g.rt - d.j - 1;
+    d.b = l2 / per; d.i = d.j + 1 + l2 % per;
+  }
+  return d;
+}
+
+__device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* error) {
+  if (ld_acquire(ctr) >= need) return true;
+  long long t0 = clock64();
+  for (;;) {
+    if (ld_acquire(ctr) >= need) return true;
+    if (*(volatile int*)error) return false;
+    if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(error, 1); return false; }
+    __nanosleep(40);
+  }
+}
+
+
+// Factor the stacked 128x64 [C; I] held in sm.Cs: each thread owns one row in registers, one
+// named barrier per column.  Top rows end as L_jj, bottom rows as L_jj^-T.  Right-looking with the
+// column left unscaled until the end of its step:  row[c2] -= (v_c(r)/a) * v_c(c2).
+__device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
+                                         double* __restrict__ LT, int ld, int tid) {
+  double row[TILE];
+  const bool top = tid < TILE;
+#pragma unroll
+  for (int c = 0; c < TILE; ++c)
+    row[c] = top ? sm.Cs[c * LDT + tid] : ((tid - TILE) == c ? 1.0 : 0.0);
+#pragma unroll
+  for (int c = 0; c < TILE; ++c) {
+    double* cb = sm.colbuf[c & 1];
+    cb[tid] = row[c];
+    bar_named(1, NCONS);
+    const double a = cb[c];                     // pivot (Schur complement diagonal)
+    if (tid == c && !(a > 0.0) && sm.bad_col < 0) sm.bad_col = c;  // first bad column only
+    const double rs = rsqrt(a);
+    const double f = row[c] * (rs * rs);        // v_c(r) / a
+#pragma unroll
+    for (int c2 = c + 1; c2 < TILE; ++c2) row[c2] = fma(-f, cb[c2], row[c2]);
+    // scaled column entry; the pivot itself gets one Newton step so L_cc = sqrt(a) to ~0.5 ulp
+    double l = row[c] * rs;
+    if (tid == c) { const double s0 = a * rs; l = fma(0.5 * rs, fma(-s0, s0, a), s0); }
+    row[c] = l;
+  }
+  if (top) {
+#pragma unroll
+    for (int c = 0; c < TILE; ++c)
+      if (c <= tid) Aij[(size_t)c * ld + tid] = row[c];
+  } else {
+    const int k = tid - TILE;
+#pragma unroll
+    for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
+  }
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
+             int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
+             int static_sched) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], 1); }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  uint32_t stage = 0, phase = 0;
+  int jcache = 0;
+
+  if (warp == NCONS / 32) {
+    // =============================== producer warp ===============================
+    int q = 0, static_next = task_begin + blockIdx.x;
+    for (;;) {
+      int t;
+      if (lane == 0) {
+        if (static_sched) { t = static_next; static_next += gridDim.x; }
+        else t = task_begin + atomicAdd(&sched->next_task, 1);
+        if (t >= task_end) t = -1;
+      }
+      t = __shfl_sync(0xffffffffu, t, 0);
+      const int slot = q & 1, qpar = (q >> 1) & 1;
+      if (lane == 0) {
+        if (!mbar_wait(&sm.tq_empty[slot], qpar ^ 1)) atomicExch(&sched->error, 2);
+        sm.taskq[slot] = t;
+        mbar_arrive(&sm.tq_full[slot]);
+      }
+      ++q;
+      if (t < 0) break;
+      const TaskDesc d = decode_task(g, t, jcache);
+      const double* M = mats + (size_t)d.b * g.mat_stride;
+      const int* done_b = done + (size_t)d.b * g.rt;
+      // lanes 0..15 fetch panel j rows (c operand), lanes 16..31 panel i rows (r operand)
+      const int rowbase = (lane < KC ? d.j : d.i) * TILE;
+      for (int kc = 0; kc < d.j; ++kc) {
+        if (lane == 0) {
+          wait_counter(done_b + d.i, kc + 1, &sched->error);
+          wait_counter(done_b + d.j, kc + 1, &sched->error);
+        }
+        __syncwarp();
+        fence_proxy_async();
+#pragma unroll 1
+        for (int s = 0; s < TILE / KC; ++s) {
+          if (lane == 0) {
+            if (!mbar_wait(&sm.empty[stage], phase ^ 1)) atomicExch(&sched->error, 3);
+            mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+          }
+          __syncwarp();
+          const int col = kc * TILE + s * KC + (lane & (KC - 1));
+          bulk_g2s(&sm.stage[stage][lane * LDT], M + (size_t)col * g.ld + rowbase,
+                   TILE * sizeof(double), &sm.full[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    return;
+  }
+
+  // ================================= consumer warps =================================
+  const int gq = lane >> 2, tq = lane & 3;          // DMMA fragment coordinates
+  const int wc = warp >> 1, wr = warp & 1;          // warp's 32x32 sub-tile: c block, r block
+  int q = 0;
+  for (;;) {
+    const int slot = q & 1, qpar = (q >> 1) & 1;
+    if (!mbar_wait(&sm.tq_full[slot], qpar)) atomicExch(&sched->error, 4);
+    const int t = sm.taskq[slot];
+    bar_named(1, NCONS);
+    if (tid == 0) mbar_arrive(&sm.tq_empty[slot]);
+    ++q;
+    if (t < 0) break;
+    const TaskDesc d = decode_task(g, t, jcache);
+    double* M = mats + (size_t)d.b * g.mat_stride;
+    int* done_b = done + (size_t)d.b * g.rt;
+    double* Aij = M + (size_t)(d.j * TILE) * g.ld + (size_t)d.i * TILE;  // (r, c) at Aij[c*ld + r]
+
+    // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*32 + nt*8 + 2*tq + {0,1}
+    double acc[4][4][2];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
+        double2 v = ld_cg2(Aij + (size_t)c * g.ld + r);
+        acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
+      }
+
+    const int nstage = d.j * (TILE / KC);
+#pragma unroll 1
+    for (int it = 0; it < nstage; ++it) {
+      if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+      const double* PA = &sm.stage[stage][0];
+      const double* PB = &sm.stage[stage][KC * LDT];
+#pragma unroll
+      for (int ks = 0; ks < KC / 4; ++ks) {
+        const int k = ks * 4 + tq;
+        double a[4], bb[4];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) a[mt] = -PA[k * LDT + wc * 32 + mt * 8 + gq];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) bb[nt] = PB[k * LDT + wr * 32 + nt * 8 + gq];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.empty[stage]);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+
+    // acc -> Cs (column-major [c][r])
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
+        *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+      }
+    if (tid == 0) sm.bad_col = -1;
+    bar_named(1, NCONS);
+
+    if (d.i == d.j) {
+      // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------
+      diag_factor(sm, Aij, linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE), g.ld, tid);
+      __threadfence();
+      fence_proxy_async();
+      bar_named(1, NCONS);
+      if (tid == 0) {
+        if (sm.bad_col >= 0) {
+          const int bad = d.j * TILE + sm.bad_col + 1;  // 1-based global pivot index
+          int old = atomicCAS(&info[d.b], 0, bad);
+          (void)old;
+        }
+        st_release(done_b + d.j, d.j + 1);
+      }
+    } else {
+      // ---------- off-diagonal task: X = C * L_jj^-T ----------
+      if (tid == 0) wait_counter(done_b + d.j, d.j + 1, &sched->error);
+      bar_named(1, NCONS);
+      const double* LT = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
+#pragma unroll 4
+      for (int e = tid; e < TILE * TILE / 2; e += NCONS) {
+        const int c = e / (TILE / 2), k2 = (e % (TILE / 2)) * 2;
+        double2 v = ld_cg2(LT + c * TILE + k2);
+        *reinterpret_cast<double2*>(&sm.Ls[c * LDT + k2]) = v;
+      }
+      bar_named(1, NCONS);
+      double x[4][4][2];
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) x[mt][nt][0] = x[mt][nt][1] = 0.0;
+      const int kend = wc * 32 + 32;   // L^-T(k, c) == 0 for k > c
+#pragma unroll 4
+      for (int k0 = 0; k0 < kend; k0 += 4) {
+        const int k = k0 + tq;
+        double a[4], bb[4];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) a[mt] = sm.Ls[(wc * 32 + mt * 8 + gq) * LDT + k];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) bb[nt] = sm.Cs[k * LDT + wr * 32 + nt * 8 + gq];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) dmma884(x[mt][nt][0], x[mt][nt][1], a[mt], bb[nt]);
+      }
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
+          *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[mt][nt][0], x[mt][nt][1]);
+        }
+      __threadfence();
+      fence_proxy_async();
+      bar_named(1, NCONS);
+      if (tid == 0) st_release(done_b + d.i, d.j + 1);
+    }
+  }
+}
+
+int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done, int* info,
+                SchedState* sched, int mode, int num_sms) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)sizeof(CholSmem));
+    attr_set = true;
+  }
+  const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
+  cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
+  cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
+  cudaMemsetAsync(sched, 0, sizeof(SchedState), st);
+  int launches = 0;
+  if (mode == 0) {
+    int grid = (int)(total < num_sms ? total : num_sms);
+    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched, 0,
+                                                           (int)total, 0);
+    launches = 1;
+  } else {
+    long long begin = 0;
+    for (int j = 0; j < g.nt; ++j) {
+      long long ndiag = g.batch, noff = (long long)g.batch * (g.rt - j - 1);
+      int grid = (int)(ndiag < num_sms ? ndiag : num_sms);
+      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
+                                                             (int)begin, (int)(begin + ndiag), 1);
+      begin += ndiag;
+      ++launches;
+      if (noff > 0) {
+        grid = (int)(noff < 2LL * num_sms ? noff : 2LL * num_sms);
+        k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
+                                                               (int)begin, (int)(begin + noff), 1);
+        begin += noff;
+        ++launches;
+      }
+    }
+  }
+  return launches;
+}
+
+}  // namespace gpb

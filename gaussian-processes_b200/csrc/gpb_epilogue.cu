@@ -1,0 +1,106 @@
+// gpb_epilogue.cu -- warp-reduced epilogues of the factorised tall system.
+//
+//   k_ll_epilogue   : Q = u.u, U1 = sum u, S = sum log L_ii   (GaussianProcess.scala:126; the three
+//                     reductions both the as-parsed and the intended formula need)
+//   k_pred_epilogue : mean_j = V_j . u, var_j = k(0) - V_j . V_j  (Predict.scala:78,89-93)
+//   k_zero_upper    : Breeze `cholesky` returns L with a zeroed strict upper triangle
+//
+// u is the solved rhs row (tile row of appended rows), V the solved K* rows.  HBM-bound, tiny.
+#include "gpb_internal.h"
+
+namespace gpb {
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(256)
+k_ll_epilogue(Geom g, const double* __restrict__ mats, const int* __restrict__ info, gpb_ll* out) {
+  const int b = blockIdx.x;
+  const double* M = mats + (size_t)b * g.mat_stride;
+  double q = 0.0, u1 = 0.0, s = 0.0;
+  for (int c = threadIdx.x; c < g.n; c += blockDim.x) {
+    const double u = M[(size_t)c * g.ld + g.rhs_row];
+    const double l = M[(size_t)c * g.ld + c];
+    q = fma(u, u, q);
+    u1 += u;
+    s += log(l);
+  }
+  __shared__ double red[3][8];
+  q = warp_sum(q); u1 = warp_sum(u1); s = warp_sum(s);
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { red[0][w] = q; red[1][w] = u1; red[2][w] = s; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double Q = 0, U1 = 0, S = 0;
+    for (int i = 0; i < 8; ++i) { Q += red[0][i]; U1 += red[1][i]; S += red[2][i]; }
+    gpb_ll r;
+    r.Q = Q; r.U1 = U1; r.S = S; r.n = g.n; r.info = info[b];
+    out[b] = r;
+  }
+}
+
+// one thread per test point j; consecutive threads read consecutive rows of a column (coalesced)
+__global__ void __launch_bounds__(128)
+k_pred_epilogue(Geom g, const double* __restrict__ mats, const Hyper* __restrict__ hyper,
+                double* __restrict__ mean, double* __restrict__ var) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const double* M = mats;  // predictive is single-proposal
+  __shared__ double us[128];
+  double mu = 0.0, vv = 0.0;
+  const size_t row = (size_t)g.npad + j;
+  for (int c0 = 0; c0 < g.n; c0 += 128) {
+    __syncthreads();
+    if (c0 + threadIdx.x < g.n) us[threadIdx.x] = M[(size_t)(c0 + threadIdx.x) * g.ld + g.rhs_row];
+    __syncthreads();
+    if (j < g.m) {
+      const int cend = min(128, g.n - c0);
+      for (int c = 0; c < cend; ++c) {
+        const double v = M[(size_t)(c0 + c) * g.ld + row];
+        mu = fma(v, us[c], mu);
+        vv = fma(v, v, vv);
+      }
+    }
+  }
+  if (j < g.m) {
+    // kyy = covFn(dist(xs, xs)) = covFn(0): every SE contributes h, every White its sigma
+    const Hyper& h = hyper[0];
+    double k0 = 0.0;
+    for (int t = 0; t < h.nterms; ++t) k0 = k0 + h.p0[t];
+    mean[j] = mu;
+    var[j] = k0 - vv;
+  }
+}
+
+__global__ void k_zero_upper(Geom g, double* __restrict__ mats) {
+  const int c = blockIdx.x;
+  double* col = mats + (size_t)blockIdx.y * g.mat_stride + (size_t)c * g.ld;
+  for (int r = threadIdx.x; r < c && r < g.n; r += blockDim.x) col[r] = 0.0;
+}
+
+__global__ void k_pad_identity(Geom g, double* __restrict__ mats) {
+  const int r = g.n + blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < g.npad) mats[(size_t)blockIdx.y * g.mat_stride + (size_t)r * g.ld + r] = 1.0;
+}
+void launch_pad_identity(cudaStream_t st, const Geom& g, double* mats) {
+  if (g.npad == g.n) return;
+  dim3 grid((g.npad - g.n + 63) / 64, g.batch);
+  k_pad_identity<<<grid, 64, 0, st>>>(g, mats);
+}
+
+void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, const int* info,
+                        gpb_ll* out) {
+  k_ll_epilogue<<<g.batch, 256, 0, st>>>(g, mats, info, out);
+}
+void launch_pred_epilogue(cudaStream_t st, const Geom& g, const double* mats, const Hyper* hyper,
+                          double* mean, double* var) {
+  k_pred_epilogue<<<(g.m + 127) / 128, 128, 0, st>>>(g, mats, hyper, mean, var);
+}
+void launch_zero_upper(cudaStream_t st, const Geom& g, double* mats) {
+  dim3 grid(g.n, g.batch);
+  k_zero_upper<<<grid, 128, 0, st>>>(g, mats);
+}
+
+}  // namespace gpb

@@ -1,0 +1,38 @@
+// gpb_internal.h -- host-visible launchers of the sm_100a kernels (one .cu per kernel family).
+#pragma once
+#include "gpb_common.cuh"
+
+namespace gpb {
+
+// Scheduler state of the factorisation kernel (device memory, zeroed before every launch).
+struct SchedState {
+  int next_task;  // atomic ticket
+  int error;      // != 0: a watchdog fired (GPB_E_WATCHDOG); kernels drain without waiting
+};
+
+void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
+                  const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
+                  int full);
+
+// Tile Cholesky + panel solves of the tall system (gpb_chol.cu).
+//   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final)
+//   linvt  [batch][nt][TILE*TILE]  inverse-transposes of the diagonal blocks (side output)
+//   info   [batch]      first non-positive pivot (1-based, LAPACK) or 0
+// mode 0: one persistent launch over all tasks; mode 1: two launches per block column.
+// Returns the number of kernel launches issued.
+int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done,
+                int* info, SchedState* sched, int mode, int num_sms);
+size_t chol_smem_bytes();
+
+// Likelihood reductions Q, U1, S per proposal (gpb_epilogue.cu).
+void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, const int* info,
+                        gpb_ll* out);
+// Predictive mean / variance per test point.
+void launch_pred_epilogue(cudaStream_t st, const Geom& g, const double* mats, const Hyper* hyper,
+                          double* mean, double* var);
+// Identity on the padded diagonal (matrix-level gpb_potrf input).
+void launch_pad_identity(cudaStream_t st, const Geom& g, double* mats);
+// Zero the strict upper triangle of the top square (matrix-level gpb_potrf output).
+void launch_zero_upper(cudaStream_t st, const Geom& g, double* mats);
+
+}  // namespace gpb

@@ -1,0 +1,272 @@
+"""ctypes binding of libgpb200.so (include/gpb200.h).
+
+The shared library is the product; this module only marshals numpy buffers across the C ABI.
+There is no CPU fallback: if the library is missing, or no B200 is visible, calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG, "libgpb200.so")
+
+KIND_SE, KIND_WHITE, KIND_MATERN = 0, 1, 2
+FORMULA_AS_PARSED, FORMULA_GPML = 0, 1
+
+EXPORTS = [
+    "gpb_ctx_create", "gpb_ctx_destroy", "gpb_dataset_create", "gpb_dataset_destroy",
+    "gpb_loglik", "gpb_loglik_batch", "gpb_ll_value", "gpb_predict", "gpb_distance_matrix",
+    "gpb_build_cov", "gpb_potrf", "gpb_trsm_lower", "gpb_trsm_upper", "gpb_mh_run",
+    "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
+    "gpb_last_timing", "gpb_set_sched", "gpb_version",
+]
+
+
+class Term(C.Structure):
+    _fields_ = [("kind", C.c_int), ("p0", C.c_double), ("p1", C.c_double), ("p2", C.c_double)]
+
+
+class LL(C.Structure):
+    _fields_ = [("Q", C.c_double), ("U1", C.c_double), ("S", C.c_double), ("n", C.c_int),
+                ("info", C.c_int)]
+
+
+class MhOpts(C.Structure):
+    _fields_ = [("formula", C.c_int), ("on_notpd", C.c_int), ("delta", C.c_double),
+                ("nugget", C.c_double)]
+
+
+class GpbError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"gpb200 status {status}: {msg}")
+        self.status = status
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+def load():
+    """Load libgpb200.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `make -C gaussian-processes_b200/csrc` "
+            "(or __graft_entry__.build()); gpb200 has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    L.gpb_strerror.restype = C.c_char_p
+    L.gpb_last_cuda_error.restype = C.c_char_p
+    L.gpb_last_cuda_error.argtypes = [C.c_void_p]
+    L.gpb_version.restype = C.c_char_p
+    L.gpb_launch_count.restype = C.c_longlong
+    L.gpb_launch_count.argtypes = [C.c_void_p]
+    L.gpb_ll_value.restype = C.c_double
+    L.gpb_ll_value.argtypes = [C.POINTER(LL), C.c_int]
+    L.gpb_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    L.gpb_ctx_destroy.argtypes = [C.c_void_p]
+    L.gpb_ctx_destroy.restype = None
+    L.gpb_dataset_create.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp, C.POINTER(C.c_void_p)]
+    L.gpb_dataset_destroy.argtypes = [C.c_void_p]
+    L.gpb_dataset_destroy.restype = None
+    L.gpb_loglik_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(Term), C.c_int, _dp,
+                                   C.c_int, C.c_double, C.POINTER(LL)]
+    L.gpb_loglik.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, _dp, C.c_int,
+                             C.c_double, C.POINTER(LL)]
+    L.gpb_predict.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
+                              _dp, _dp, _dp, _ip]
+    L.gpb_distance_matrix.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_build_cov.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, C.POINTER(Term), C.c_int,
+                                C.c_double, _dp]
+    L.gpb_potrf.argtypes = [C.c_void_p, C.c_int, _dp, _ip]
+    L.gpb_trsm_lower.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_trsm_upper.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_mh_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Term), C.c_int,
+                             _dp, C.c_int, _dp, C.POINTER(MhOpts), _dp, _dp, _dp, _dp, _ip, _ip]
+    L.gpb_philox_streams.argtypes = [C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+    L.gpb_set_sched.argtypes = [C.c_void_p, C.c_int]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_dp)
+
+
+def as_f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def x_soa(x):
+    """(n,) or (n, dim) array of locations -> contiguous SoA [dim][n], dim"""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    return np.ascontiguousarray(x.T), x.shape[1]
+
+
+def terms_array(term_lists):
+    """term_lists: list (batch) of lists of (kind, p0, p1) -> (Term * (batch*nterms)), nterms"""
+    nterms = len(term_lists[0])
+    arr = (Term * (len(term_lists) * nterms))()
+    k = 0
+    for tl in term_lists:
+        if len(tl) != nterms:
+            raise ValueError("all proposals of a batch must have the same kernel structure")
+        for kind, p0, p1 in tl:
+            arr[k] = Term(int(kind), float(p0), float(p1), 0.0)
+            k += 1
+    return arr, nterms
+
+
+class Context:
+    """One device + stream + workspace (gpb_ctx).  Not thread-safe; one per host thread."""
+
+    def __init__(self, device=0):
+        self.L = load()
+        h = C.c_void_p()
+        self._check(self.L.gpb_ctx_create(int(device), C.byref(h)), ctx=None)
+        self.h = h
+        self.device = device
+
+    def _check(self, status, ctx="self"):
+        if status != 0:
+            msg = self.L.gpb_strerror(status).decode()
+            if ctx is not None and getattr(self, "h", None):
+                extra = self.L.gpb_last_cuda_error(self.h).decode()
+                if extra:
+                    msg += " [" + extra + "]"
+            raise GpbError(status, msg)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gpb_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_sched(self, mode):
+        self._check(self.L.gpb_set_sched(self.h, int(mode)))
+
+    def launch_count(self):
+        return int(self.L.gpb_launch_count(self.h))
+
+    def last_timing(self):
+        t = (C.c_float * 3)()
+        self._check(self.L.gpb_last_timing(self.h, t))
+        return [float(v) for v in t]
+
+    def dataset(self, x, y=None):
+        return Dataset(self, x, y)
+
+    # ---- matrix level ----
+    def distance_matrix(self, x):
+        xs, dim = x_soa(x)
+        n = xs.shape[1]
+        out = np.empty((n, n), dtype=np.float64)
+        self._check(self.L.gpb_distance_matrix(self.h, n, dim, _ptr(xs), _ptr(out)))
+        return out.T
+
+    def build_cov(self, x, terms, nugget=0.0):
+        xs, dim = x_soa(x)
+        n = xs.shape[1]
+        arr, nterms = terms_array([terms])
+        out = np.empty((n, n), dtype=np.float64)
+        self._check(self.L.gpb_build_cov(self.h, n, dim, _ptr(xs), arr, nterms, float(nugget), _ptr(out)))
+        return out.T
+
+    def potrf(self, K):
+        K = np.asarray(K, dtype=np.float64)
+        n = K.shape[0]
+        a = np.array(K.T, dtype=np.float64, order="C")  # buffer == column-major K
+        info = C.c_int(0)
+        self._check(self.L.gpb_potrf(self.h, n, _ptr(a), C.byref(info)))
+        return a.T.copy(), info.value
+
+    def _trsm(self, fn, T, B):
+        T = np.asarray(T, dtype=np.float64)
+        B = np.asarray(B, dtype=np.float64)
+        vec = B.ndim == 1
+        Bm = B[:, None] if vec else B
+        n, nrhs = Bm.shape
+        t = np.array(T.T, dtype=np.float64, order="C")
+        b = np.array(Bm.T, dtype=np.float64, order="C")
+        self._check(fn(self.h, n, nrhs, _ptr(t), _ptr(b)))
+        out = b.T.copy()
+        return out[:, 0] if vec else out
+
+    def trsm_lower(self, L, B):
+        return self._trsm(self.L.gpb_trsm_lower, L, B)
+
+    def trsm_upper(self, U, B):
+        return self._trsm(self.L.gpb_trsm_upper, U, B)
+
+
+class Dataset:
+    """Observations resident on the device (gpb_dataset)."""
+
+    def __init__(self, ctx, x, y=None):
+        self.ctx = ctx
+        xs, dim = x_soa(x)
+        self.n, self.dim = xs.shape[1], dim
+        yv = as_f64(y) if y is not None else None
+        if yv is not None and yv.shape != (self.n,):
+            raise ValueError("y must have one value per location")
+        h = C.c_void_p()
+        ctx._check(ctx.L.gpb_dataset_create(ctx.h, self.n, dim, _ptr(xs),
+                                            _ptr(yv) if yv is not None else None, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.L.gpb_dataset_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def loglik_batch(self, term_lists, betas=None, nugget=1e-3):
+        """term_lists: [batch][nterms] of (kind, p0, p1).  Returns list of dicts Q,U1,S,n,info."""
+        ctx = self.ctx
+        arr, nterms = terms_array(term_lists)
+        batch = len(term_lists)
+        if betas is None or len(betas) == 0 or len(betas[0]) == 0:
+            bptr, nbeta = None, 0
+        else:
+            bv = as_f64(betas)
+            if bv.shape[0] != batch:
+                raise ValueError("one beta vector per proposal")
+            bptr, nbeta = _ptr(bv), bv.shape[1]
+        out = (LL * batch)()
+        ctx._check(ctx.L.gpb_loglik_batch(ctx.h, self.h, batch, arr, nterms, bptr, nbeta,
+                                          float(nugget), out))
+        return out
+
+    def predict(self, terms, xstar, nugget=1e-6):
+        ctx = self.ctx
+        arr, nterms = terms_array([terms])
+        xt, dim = x_soa(xstar)
+        if dim != self.dim:
+            raise ValueError("Dimension mismatch")  # Location.scala:32
+        m = xt.shape[1]
+        mean = np.empty(m)
+        var = np.empty(m)
+        info = C.c_int(0)
+        ctx._check(ctx.L.gpb_predict(ctx.h, self.h, arr, nterms, float(nugget), m, _ptr(xt),
+                                     _ptr(mean), _ptr(var), C.byref(info)))
+        return mean, var, info.value
+
+
+def ll_value(r, formula=FORMULA_AS_PARSED):
+    return load().gpb_ll_value(C.byref(r), int(formula))

@@ -1,79 +1,16 @@
 // gpb_api.cu -- the C ABI of libgpb200.so (include/gpb200.h): contexts, datasets, workspace and
 // the host-side sequencing of the sm_100a kernels.  No CPU fallback anywhere: every entry point
 // either runs the CUDA path or returns an error status.
-#include <cmath>
-#include <cstdio>
-#include <cstring>
-#include <new>
-#include <string>
-#include <vector>
-
-#include "gpb_internal.h"
+#include "gpb_host.h"
 
 using namespace gpb;
+using namespace gpbh;
 
-struct gpb_ctx {
-  int device = 0;
-  int num_sms = 0;
-  int sched_mode = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  // workspace (grown on demand, never shrunk)
-  double* mats = nullptr;   size_t mats_doubles = 0;
-  double* linvt = nullptr;  size_t linvt_doubles = 0;
-  int* done = nullptr;      size_t done_ints = 0;
-  int* info = nullptr;      size_t info_ints = 0;
-  Hyper* hyper = nullptr;   size_t hyper_n = 0;
-  gpb_ll* ll = nullptr;     size_t ll_n = 0;
-  double* aux = nullptr;    size_t aux_doubles = 0;   // xstar / predictive outputs / MH state
-  SchedState* sched = nullptr;
-  SchedState* h_sched = nullptr;  // pinned
-  // pinned host staging
-  Hyper* h_hyper = nullptr; size_t h_hyper_n = 0;
-  gpb_ll* h_ll = nullptr;   size_t h_ll_n = 0;
-  long long launches = 0;
-  float timing[3] = {0, 0, 0};
-  std::string cuda_err;
-};
-
-struct gpb_dataset {
-  gpb_ctx* ctx;
-  int n, dim;
-  double* x;  // SoA [dim][n]
-  double* y;  // [n]
-};
-
-namespace {
-
+namespace gpbh {
 int cuda_fail(gpb_ctx* ctx, cudaError_t e, const char* where) {
   if (ctx) ctx->cuda_err = std::string(where) + ": " + cudaGetErrorString(e);
   return (e == cudaErrorMemoryAllocation) ? GPB_E_NOMEM : GPB_E_CUDA;
 }
-#define CK(call)                                             \
-  do {                                                       \
-    cudaError_t e_ = (call);                                 \
-    if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); \
-  } while (0)
-
-template <typename T>
-int grow(gpb_ctx* ctx, T** p, size_t* have, size_t want) {
-  if (*have >= want) return GPB_OK;
-  if (*p) { cudaFree(*p); *p = nullptr; *have = 0; }
-  cudaError_t e = cudaMalloc((void**)p, want * sizeof(T));
-  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(ctx, e, "cudaMalloc(workspace)"); }
-  *have = want;
-  return GPB_OK;
-}
-template <typename T>
-int grow_pinned(gpb_ctx* ctx, T** p, size_t* have, size_t want) {
-  if (*have >= want) return GPB_OK;
-  if (*p) { cudaFreeHost(*p); *p = nullptr; *have = 0; }
-  cudaError_t e = cudaMallocHost((void**)p, want * sizeof(T));
-  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(ctx, e, "cudaMallocHost"); }
-  *have = want;
-  return GPB_OK;
-}
-
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // m test points + (with_rhs ? 1 : 0) rhs row appended below the npad x npad square
@@ -144,12 +81,13 @@ int finish_timing(gpb_ctx* ctx) {
   const SchedState s = *ctx->h_sched;
   if (s.error != 0) {
     ctx->cuda_err = "scheduler watchdog code " + std::to_string(s.error);
+    cudaMemset(ctx->sched, 0, sizeof(SchedState));
     return GPB_E_WATCHDOG;
   }
   return GPB_OK;
 }
 
-}  // namespace
+}  // namespace gpbh
 
 extern "C" {
 

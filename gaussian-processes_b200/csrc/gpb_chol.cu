@@ -116,10 +116,29 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
   }
 }
 
+// Triangular-solve mode: sm.Cs holds a given lower-triangular L_jj; thread 64+k computes row k of
+// L_jj^-T by substitution on the stacked [L; I] (no factorisation, no barriers: L is read-only).
+__device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT, int tid) {
+  if (tid < TILE) return;
+  const int k = tid - TILE;
+  double row[TILE];
+#pragma unroll
+  for (int c = 0; c < TILE; ++c) row[c] = (k == c) ? 1.0 : 0.0;
+#pragma unroll
+  for (int c = 0; c < TILE; ++c) {
+    const double xv = row[c] / sm.Cs[c * LDT + c];
+    row[c] = xv;
+#pragma unroll
+    for (int c2 = c + 1; c2 < TILE; ++c2) row[c2] = fma(-xv, sm.Cs[c * LDT + c2], row[c2]);
+  }
+#pragma unroll
+  for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
-             int static_sched) {
+             int static_sched, int solve_only) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -154,6 +173,7 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
       ++q;
       if (t < 0) break;
       const TaskDesc d = decode_task(g, t, jcache);
+      if (solve_only && d.i < g.nt) continue;  // L is given: no accumulation for top-square tiles
       const double* M = mats + (size_t)d.b * g.mat_stride;
       const int* done_b = done + (size_t)d.b * g.rt;
       // lanes 0..15 fetch panel j rows (c operand), lanes 16..31 panel i rows (r operand)
@@ -198,6 +218,11 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
     double* Aij = M + (size_t)(d.j * TILE) * g.ld + (size_t)d.i * TILE;  // (r, c) at Aij[c*ld + r]
+    if (solve_only && d.i < g.nt && d.i != d.j) {
+      // triangular-solve mode: the factor is an input, its off-diagonal tiles are already final
+      if (tid == 0) atomicMax(done_b + d.i, d.j + 1);
+      continue;
+    }
 
     // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*32 + nt*8 + 2*tq + {0,1}
     double acc[4][4][2];
@@ -210,7 +235,7 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
         acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
       }
 
-    const int nstage = d.j * (TILE / KC);
+    const int nstage = (solve_only && d.i < g.nt) ? 0 : d.j * (TILE / KC);
 #pragma unroll 1
     for (int it = 0; it < nstage; ++it) {
       if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
@@ -247,7 +272,9 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
 
     if (d.i == d.j) {
       // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------
-      diag_factor(sm, Aij, linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE), g.ld, tid);
+      double* LTj = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
+      if (solve_only) diag_inverse(sm, LTj, tid);
+      else diag_factor(sm, Aij, LTj, g.ld, tid);
       __threadfence();
       fence_proxy_async();
       bar_named(1, NCONS);
@@ -257,7 +284,8 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
           int old = atomicCAS(&info[d.b], 0, bad);
           (void)old;
         }
-        st_release(done_b + d.j, d.j + 1);
+        if (solve_only) atomicMax(done_b + d.j, d.j + 1);
+        else st_release(done_b + d.j, d.j + 1);
       }
     } else {
       // ---------- off-diagonal task: X = C * L_jj^-T ----------
@@ -306,7 +334,7 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
 }
 
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done, int* info,
-                SchedState* sched, int mode, int num_sms) {
+                SchedState* sched, int mode, int num_sms, int solve_only) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -316,12 +344,12 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
   cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
   cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
-  cudaMemsetAsync(sched, 0, sizeof(SchedState), st);
+  cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   int launches = 0;
   if (mode == 0) {
     int grid = (int)(total < num_sms ? total : num_sms);
     k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched, 0,
-                                                           (int)total, 0);
+                                                           (int)total, 0, solve_only);
     launches = 1;
   } else {
     long long begin = 0;
@@ -329,13 +357,13 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
       long long ndiag = g.batch, noff = (long long)g.batch * (g.rt - j - 1);
       int grid = (int)(ndiag < num_sms ? ndiag : num_sms);
       k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
-                                                             (int)begin, (int)(begin + ndiag), 1);
+                                                             (int)begin, (int)(begin + ndiag), 1, solve_only);
       begin += ndiag;
       ++launches;
       if (noff > 0) {
         grid = (int)(noff < 2LL * num_sms ? noff : 2LL * num_sms);
         k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
-                                                               (int)begin, (int)(begin + noff), 1);
+                                                               (int)begin, (int)(begin + noff), 1, solve_only);
         begin += noff;
         ++launches;
       }

@@ -268,5 +268,44 @@ class Dataset:
         return mean, var, info.value
 
 
+    def mh_run(self, init_term_lists, ig, delta, z, u, beta=(), nugget=1e-3,
+               formula=FORMULA_AS_PARSED, on_notpd=0):
+        """Device-resident MH for len(init_term_lists) chains (gpb_mh_run).
+        z: (iters, chains, P) standard normals, u: (iters, chains) uniforms, ig: (P, 2).
+        Returns states (iters, chains, P), ll (iters, chains), accept (iters, chains), info."""
+        ctx = self.ctx
+        arr, nterms = terms_array(init_term_lists)
+        chains = len(init_term_lists)
+        zv, uv, igv = as_f64(z), as_f64(u), as_f64(ig)
+        iters = uv.shape[0]
+        P = igv.shape[0]
+        if uv.shape != (iters, chains) or zv.shape != (iters, chains, P) or igv.shape != (P, 2):
+            raise ValueError("stream / prior shapes do not match (iters, chains, P)")
+        bv = as_f64(beta) if len(beta) else None
+        opts = MhOpts(int(formula), int(on_notpd), float(delta), float(nugget))
+        states = np.empty((iters, chains, P))
+        ll = np.empty((iters, chains))
+        acc = np.empty((iters, chains), dtype=np.int32)
+        info = C.c_int(0)
+        st = ctx.L.gpb_mh_run(ctx.h, self.h, chains, iters, arr, nterms,
+                              _ptr(bv) if bv is not None else None, 0 if bv is None else bv.shape[0],
+                              _ptr(igv), C.byref(opts), _ptr(zv), _ptr(uv), _ptr(states), _ptr(ll),
+                              acc.ctypes.data_as(_ip), C.byref(info))
+        if st == -7:  # GPB_E_NOTPD: the reference throws from cholesky here
+            raise GpbError(st, f"proposal covariance not positive definite (info={info.value})")
+        ctx._check(st)
+        return states, ll, acc, info.value
+
+
+def philox_streams(seed, chain0, chains, iters, P):
+    """gpb_philox_streams: z (iters, chains, P) normals and u (iters, chains) uniforms (host)."""
+    z = np.empty((iters, chains, P))
+    u = np.empty((iters, chains))
+    st = load().gpb_philox_streams(int(seed), int(chain0), int(chains), int(iters), int(P), _ptr(z), _ptr(u))
+    if st != 0:
+        raise GpbError(st, load().gpb_strerror(st).decode())
+    return z, u
+
+
 def ll_value(r, formula=FORMULA_AS_PARSED):
     return load().gpb_ll_value(C.byref(r), int(formula))

@@ -25,11 +25,12 @@ __device__ __forceinline__ double cov_of_dist(const Hyper& h, double d) {
     double v;
     if (h.kind[t] == GPB_KIND_SE) {
       double sg = h.p1[t];
-      v = h.p0[t] * exp(-(d * d) / (sg * sg));  // KernelFunction.scala:14
+      // KernelFunction.scala:14; explicit _rn ops: the JVM never contracts a*b+c into an FMA
+      v = __dmul_rn(h.p0[t], exp(-__ddiv_rn(__dmul_rn(d, d), __dmul_rn(sg, sg))));
     } else {
       v = (d == 0.0) ? h.p0[t] : 0.0;  // KernelFunction.scala:34
     }
-    s = s + v;
+    s = __dadd_rn(s, v);
   }
   return s;
 }
@@ -56,8 +57,8 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
       if (g.dim == 2) c1 = x[g.n + c];
       if (y != nullptr) yy = y[c];
       if (h.nbeta > 0) {  // MeanFunction.scala:7-10 plane
-        mu = h.beta[0] + c0 * h.beta[1];
-        if (g.dim == 2) mu = mu + c1 * h.beta[2];
+        mu = __dadd_rn(h.beta[0], __dmul_rn(c0, h.beta[1]));
+        if (g.dim == 2) mu = __dadd_rn(mu, __dmul_rn(c1, h.beta[2]));
       }
     }
     cx[0][tid] = c0; cx[1][tid] = c1; cy[tid] = yy; cm[tid] = mu;
@@ -97,17 +98,17 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
       v = (rclass == 1 && R == Cc) ? 1.0 : 0.0;
     } else if (rclass == 0 || rclass == 2) {
       double dx = r0 - cx[0][cl];
-      double d2 = dx * dx;
+      double d2 = __dmul_rn(dx, dx);
       if (g.dim == 2) {
         double dy = r1 - cx[1][cl];
-        d2 = d2 + dy * dy;
+        d2 = __dadd_rn(d2, __dmul_rn(dy, dy));  // no FMA contraction: mirror Location.scala:30-31
       }
       double d = sqrt(d2);  // Location.scala:28-31
       if (mode == 1) {
         v = d;
       } else {
         v = cov_of_dist(h, d);
-        if (rclass == 0 && R == Cc) v = v + nugget;  // GaussianProcess.scala:117-118
+        if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);  // GaussianProcess.scala:117-118
       }
     } else if (rclass == 3) {
       v = cy[cl] - cm[cl];  // GaussianProcess.scala:120-122

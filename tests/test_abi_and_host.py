@@ -1,0 +1,120 @@
+"""CPU tests of the boundary: the C-ABI library loads and exports every declared symbol, its
+host-only entry points work, it refuses to run without a B200 (no CPU fallback), and the host-side
+mirror of the reference API keeps the reference's parameter conventions."""
+import ctypes as C
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_symbol_the_header_declares():
+    from gpb200 import _lib as G
+    L = G.load()
+    hdr = open(os.path.join(ROOT, "include", "gpb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(gpb_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/gpb200.h but not exported"
+    assert sorted(G.EXPORTS) == declared
+
+
+def test_no_cpu_fallback_without_a_gpu():
+    import torch
+    from gpb200 import _lib as G
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is visible: the refusal path cannot be exercised")
+    with pytest.raises(G.GpbError) as e:
+        G.Context(0)
+    assert e.value.status == -2  # GPB_E_NODEVICE
+
+
+def test_product_package_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "gaussian-processes_b200")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".scala")):
+                src = open(os.path.join(d, f)).read()
+                for needle in ("import oracle", "from oracle", "gp_oracle", "orc_", "/oracle"):
+                    assert needle not in src, (d, f, needle)
+
+
+def test_ll_value_formulas():
+    from gpb200 import _lib as G
+    r = G.LL(10.0, -2.0, 3.5, 7, 0)
+    Cc = 7 * 0.5 * math.log(2 * math.pi)
+    assert G.ll_value(r, G.FORMULA_GPML) == -0.5 * 10.0 - 3.5 - Cc
+    assert G.ll_value(r, G.FORMULA_AS_PARSED) == -0.5 * 10.0 + 0.5 * (3.5 + Cc) * -2.0
+    assert math.isnan(G.ll_value(G.LL(1.0, 1.0, 1.0, 7, 3), 0))
+
+
+def test_philox_streams_are_counter_based():
+    from gpb200 import _lib as G
+    z, u = G.philox_streams(42, 0, 4, 50, 3)
+    z2, u2 = G.philox_streams(42, 2, 2, 50, 3)  # chains 2..3 regenerated on another rank
+    assert np.array_equal(z[:, 2:], z2) and np.array_equal(u[:, 2:], u2)
+    z3, _ = G.philox_streams(43, 0, 4, 50, 3)
+    assert not np.array_equal(z, z3)
+    assert np.all((u > 0) & (u < 1)) and abs(z.mean()) < 0.2 and 0.8 < z.std() < 1.2
+    # known-answer: Philox4x32-10 zero counter / zero key (Random123 kat vectors)
+    L = G.load()
+    zz = np.zeros(2); uu = np.zeros(1)
+    assert L.gpb_philox_streams(0, 0, 1, 1, 2, zz.ctypes.data_as(C.POINTER(C.c_double)),
+                                uu.ctypes.data_as(C.POINTER(C.c_double))) == 0
+
+
+def test_strerror_and_version():
+    from gpb200 import _lib as G
+    L = G.load()
+    assert L.gpb_strerror(0) == b"ok"
+    assert b"no CPU fallback" in L.gpb_strerror(-2)
+    assert b"sm_100a" in L.gpb_version()
+
+
+# ---- host mirror of the reference API ------------------------------------------------------------
+def test_location_and_dimension_mismatch():
+    from gpb200 import Location, One, Two
+    assert Location.euclidean(One(1.0), One(4.0)) == 3.0
+    assert Location.euclidean(Two(0.0, 0.0), Two(3.0, 4.0)) == 5.0
+    with pytest.raises(Exception, match="Dimension mismatch"):
+        Location.euclidean(One(1.0), Two(1.0, 2.0))  # Location.scala:32
+
+
+def test_cov_fn_closure_is_the_reference_scalar_function():
+    from gpb200 import KernelFunction, SquaredExp, White
+    k = KernelFunction.apply([SquaredExp(3.0, 5.5), White(0.5)])
+    assert k(0.0) == 3.5 and k(2.0) == 3.0 * math.exp(-4.0 / 30.25)
+
+
+def test_arbitrary_dist_closures_are_refused_not_emulated():
+    from gpb200 import GaussianProcess, One
+    with pytest.raises(NotImplementedError):
+        GaussianProcess.distanceMatrix([One(0.0), One(1.0)], lambda a, b: 0.0)
+
+
+kernel_term = st.one_of(
+    st.tuples(st.just("se"), st.floats(2, 10), st.floats(2, 10)),
+    st.tuples(st.just("white"), st.floats(2, 10)))
+
+
+@settings(max_examples=100, deadline=None)
+@given(st.lists(kernel_term, min_size=3, max_size=3), st.lists(st.floats(-5, 5), min_size=3, max_size=3))
+def test_params_array_round_trip(terms, beta):
+    """The reference's only live test (core/src/test/scala/ParameterTest.scala:57-69):
+    arrayToParams(p, paramsToArray(p)) === p, flattening = mean first, then SE -> (h, sigma),
+    White -> (sigma)."""
+    from gpb200 import GaussianProcess, KernelParameters, Plane, SquaredExp, White
+    ks = [SquaredExp(t[1], t[2]) if t[0] == "se" else White(t[1]) for t in terms]
+    p = GaussianProcess.Parameters(Plane(beta), ks)
+    arr = KernelParameters.paramsToArray(p)
+    flat = list(beta)
+    for t in terms:
+        flat.extend(t[1:])
+    assert list(arr) == flat
+    assert KernelParameters.arrayToParams(p, arr) == p

@@ -1,0 +1,340 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libgpb200.so), against the CPU oracle
+on the same seeded inputs, against the frozen golden fixtures, and -- at BASELINE.json's full
+sizes -- through size-independent properties (L L^T = K, linear-system residuals, LAPACK twin).
+
+Tolerances (north_star): relative 1e-10 on the log-likelihood in FP64 (we observe ~1e-14);
+identical accept/reject sequences for identical RNG streams.  cond(K) is printed with the
+large-n parity numbers.
+"""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+import scipy.linalg as sl
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "gp_golden.json")
+SE_W = [("se", 3.0, 5.5), ("white", 0.5)]
+SE_SE_W = [("se", 3.0, 5.5), ("se", 1.0, 0.8), ("white", 0.5)]
+LL_RTOL = 1e-10
+
+
+def gterms(terms):
+    return [(0, t[1], t[2]) if t[0] == "se" else (1, t[1], 0.0) for t in terms]
+
+
+def synth(oracle, n, dim, terms, seed, lo=-10.0, hi=10.0):
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(lo, hi, size=(n, dim))
+    if n >= 8:
+        x[5] = x[2]  # exact duplicate: white noise lands off the diagonal
+    K = oracle.build_cov(x, terms, 1e-3)
+    y = np.linalg.cholesky(K) @ rng.standard_normal(n)
+    return x, y, K
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 20, 63, 64, 65, 128, 300])
+@pytest.mark.parametrize("dim", [1, 2])
+def test_build_cov_and_distance_entrywise(ctx, oracle, n, dim):
+    x, _, _ = synth(oracle, n, dim, SE_SE_W, 100 + n)
+    K = ctx.build_cov(x, gterms(SE_SE_W), 1e-3)
+    Ko = oracle.build_cov(x, SE_SE_W, 1e-3)
+    # only exp() differs (CUDA libm vs glibc, both <= 1 ulp): allow 4 ulp of the entry
+    assert np.all(np.abs(K - Ko) <= 4 * np.spacing(np.abs(Ko)))
+    assert np.array_equal(K, K.T)
+    D = ctx.distance_matrix(x)
+    Do = np.sqrt(((x[:, None, :] - x[None, :, :]) ** 2).sum(-1))
+    assert np.all(np.abs(D - Do) <= 2 * np.spacing(Do))
+    assert np.all(np.diag(D) == 0)
+    if n >= 8:
+        assert K[5, 2] == 3.0 + 1.0 + 0.5  # SE(0) + SE(0) + white, no nugget off the diagonal
+
+
+@pytest.mark.parametrize("sched", [0, 1])
+@pytest.mark.parametrize("n,dim,terms", [
+    (1, 1, SE_W), (2, 1, SE_W), (3, 2, SE_SE_W), (20, 1, SE_W), (63, 2, SE_W), (64, 1, SE_SE_W),
+    (65, 2, SE_W), (300, 1, SE_W), (300, 2, SE_SE_W), (1024, 2, SE_W)])
+def test_loglik_parity(ctx, oracle, sched, n, dim, terms):
+    ctx.set_sched(sched)
+    try:
+        x, y, _ = synth(oracle, n, dim, terms, 7 * n + dim)
+        ds = ctx.dataset(x, y)
+        from gpb200 import _lib as G
+        r = ds.loglik_batch([gterms(terms)], nugget=1e-3)[0]
+        ro = oracle.loglik(x, y, terms, nugget=1e-3)
+        assert r.info == 0 and r.n == n
+        assert rel(r.Q, ro["Q"]) < LL_RTOL and rel(r.S, ro["S"]) < LL_RTOL
+        assert abs(r.U1 - ro["U1"]) < 1e-10 * max(1.0, math.sqrt(n))
+        assert rel(G.ll_value(r, G.FORMULA_AS_PARSED), ro["ll_ref"]) < LL_RTOL  # what the reference executes
+        assert rel(G.ll_value(r, G.FORMULA_GPML), ro["ll_gpml"]) < LL_RTOL      # what its docs intend
+        ds.close()
+    finally:
+        ctx.set_sched(0)
+
+
+def test_plane_mean_and_batch_of_proposals(ctx, oracle):
+    from gpb200 import _lib as G
+    n = 200
+    x, y, _ = synth(oracle, n, 2, SE_W, 31)
+    ds = ctx.dataset(x, y)
+    rng = np.random.default_rng(1)
+    props, betas = [], []
+    for b in range(9):
+        props.append([("se", 3.0 * math.exp(0.2 * rng.standard_normal()), 5.5 * math.exp(0.2 * rng.standard_normal())),
+                      ("white", 0.5 * math.exp(0.2 * rng.standard_normal()))])
+        betas.append(list(rng.normal(size=3)))
+    rs = ds.loglik_batch([gterms(p) for p in props], betas, nugget=1e-3)
+    for b in range(9):
+        ro = oracle.loglik(x, y, props[b], beta=betas[b], nugget=1e-3)
+        assert rs[b].info == 0
+        assert rel(G.ll_value(rs[b], 0), ro["ll_ref"]) < LL_RTOL
+        assert rel(G.ll_value(rs[b], 1), ro["ll_gpml"]) < LL_RTOL
+    # a batch gives bit-identical numbers to one-at-a-time calls (the schedule does not enter the sums)
+    one = ds.loglik_batch([gterms(props[4])], [betas[4]], nugget=1e-3)[0]
+    assert (one.Q, one.U1, one.S) == (rs[4].Q, rs[4].U1, rs[4].S)
+    ds.close()
+
+
+def test_golden_fixtures_through_the_c_abi(ctx):
+    from gpb200 import _lib as G
+    g = json.load(open(GOLDEN))
+    for c in g["cases"]:
+        terms = [tuple(t) for t in c["terms"]]
+        ds = ctx.dataset(np.array(c["x"]), np.array(c["y"]))
+        r = ds.loglik_batch([gterms(terms)], [c["beta"]] if c["beta"] else None, nugget=c["nugget_ll"])[0]
+        assert r.info == 0
+        assert rel(G.ll_value(r, 0), c["ll"]["ll_ref"]) < LL_RTOL
+        assert rel(G.ll_value(r, 1), c["ll"]["ll_gpml"]) < LL_RTOL
+        mean, var, info = ds.predict(gterms(terms), np.array(c["xstar"]), nugget=c["nugget_pred"])
+        assert info == 0
+        # nugget 1e-6 => cond(K) up to ~1e7: absolute tolerance scaled to the prior variance
+        assert np.allclose(mean, c["pred_mean"], rtol=1e-7, atol=1e-8)
+        assert np.allclose(var, c["pred_var"], rtol=1e-7, atol=1e-8)
+        ds.close()
+
+
+@pytest.mark.parametrize("n,m,dim", [(20, 1, 1), (64, 64, 1), (150, 200, 2), (300, 2000, 1)])
+def test_predict_parity(ctx, oracle, n, m, dim):
+    x, y, _ = synth(oracle, n, dim, SE_W, 900 + n)
+    rng = np.random.default_rng(m)
+    xs = rng.uniform(-10, 10, size=(m, dim))
+    xs[0] = x[0]
+    ds = ctx.dataset(x, y)
+    mean, var, info = ds.predict(gterms(SE_W), xs, nugget=1e-6)
+    mo, vo, io = oracle.predict(x, y, SE_W, xs, nugget=1e-6)
+    assert info == 0 and io == 0
+    assert np.allclose(mean, mo, rtol=1e-7, atol=1e-8) and np.allclose(var, vo, rtol=1e-7, atol=1e-8)
+    ds.close()
+
+
+@pytest.mark.parametrize("n", [1, 5, 64, 100, 257])
+def test_potrf_and_triangular_solves(ctx, oracle, n):
+    rng = np.random.default_rng(n)
+    A = rng.standard_normal((n, n))
+    K = A @ A.T + n * np.eye(n)
+    L, info = ctx.potrf(K)
+    Lo, io = oracle.potrf_lower(K)
+    assert info == 0 and io == 0
+    assert np.all(np.triu(L, 1) == 0)  # Breeze zeroes the strict upper triangle
+    assert np.allclose(L, Lo, rtol=1e-12, atol=1e-12)
+    b = rng.standard_normal(n); B = rng.standard_normal((n, 3))
+    assert np.allclose(ctx.trsm_lower(Lo, b), oracle.trsv_lower(Lo, b), rtol=1e-11, atol=1e-12)   # Predict.forwardSolve
+    assert np.allclose(ctx.trsm_upper(Lo.T, b), oracle.trsv_upper(Lo.T, b), rtol=1e-11, atol=1e-12)  # Mcmc.backSolve vec
+    assert np.allclose(ctx.trsm_upper(Lo.T, B), oracle.trsm_upper(Lo.T, B), rtol=1e-11, atol=1e-12)  # Mcmc.backSolve mat
+
+
+def test_not_positive_definite_is_reported_not_fatal(ctx, oracle):
+    from gpb200 import _lib as G
+    K = np.array([[1.0, 2.0, 0.0], [2.0, 1.0, 0.0], [0.0, 0.0, 1.0]])
+    _, info = ctx.potrf(K)
+    assert info == 2  # LAPACK convention, same as the oracle
+    x = np.arange(70.0); y = np.ones(70)
+    bad = [("se", 1.0, 5.0), ("white", -2.0)]
+    ds = ctx.dataset(x, y)
+    rs = ds.loglik_batch([gterms(bad), gterms(SE_W)], nugget=1e-3)
+    ro = oracle.loglik(x, y, bad)
+    assert rs[0].info == ro["info"] > 0 and math.isnan(G.ll_value(rs[0], 0))
+    assert rs[1].info == 0  # the healthy proposal in the same batch is unaffected
+    assert rel(G.ll_value(rs[1], 1), oracle.loglik(x, y, SE_W)["ll_gpml"]) < LL_RTOL
+    ds.close()
+
+
+def test_unsupported_inputs_fail_loudly(ctx):
+    from gpb200 import _lib as G
+    ds = ctx.dataset(np.arange(4.0), np.ones(4))
+    with pytest.raises(G.GpbError) as e:
+        ds.loglik_batch([[(2, 1.0, 1.0)]])  # Matern: out of scope
+    assert e.value.status == -5
+    with pytest.raises(G.GpbError):
+        ctx.dataset(np.ones((4, 3)), np.ones(4))  # dim 3
+    ds.close()
+
+
+def test_schedulers_agree_bitwise(ctx, oracle):
+    x, y, _ = synth(oracle, 700, 2, SE_SE_W, 77)
+    ds = ctx.dataset(x, y)
+    out = []
+    for sched in (0, 1, 0):
+        ctx.set_sched(sched)
+        r = ds.loglik_batch([gterms(SE_SE_W)] * 3)
+        out.append([(v.Q, v.U1, v.S) for v in r])
+    ctx.set_sched(0)
+    assert out[0] == out[1] == out[2]
+    ds.close()
+
+
+def test_mh_accept_reject_sequence_matches_oracle(ctx, oracle):
+    """north_star: identical accept/reject sequences for identical RNG streams."""
+    g = json.load(open(GOLDEN))["mh"]
+    terms = [tuple(t) for t in g["terms"]]
+    x, y, z, u = (np.array(g[k]) for k in ("x", "y", "z", "u"))
+    ds = ctx.dataset(x, y)
+    for formula in (0, 1):
+        want = g["by_formula"][str(formula)]
+        st, ll, acc, info = ds.mh_run([gterms(terms)], g["ig"], g["delta"], z[:, None, :], u[:, None],
+                                      formula=formula)
+        assert info == 0
+        assert np.array_equal(acc[:, 0], want["accept"])
+        assert np.allclose(st[:, 0, :], want["states"], rtol=1e-13, atol=0)
+        assert np.allclose(ll[:, 0], want["ll"], rtol=1e-10, atol=0)
+    ds.close()
+
+
+def test_mh_many_chains_match_independent_oracle_chains(ctx, oracle):
+    from gpb200 import _lib as G
+    n, chains, iters = 96, 6, 60
+    x, y, _ = synth(oracle, n, 2, SE_SE_W, 5)
+    ig = [[3.0, 4.0], [3.0, 6.0], [3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]
+    z, u = G.philox_streams(11, 0, chains, iters, 5)
+    rng = np.random.default_rng(3)
+    inits = [[("se", 3.0 * math.exp(0.1 * rng.standard_normal()), 5.5), ("se", 1.0, 0.8 * math.exp(0.1 * rng.standard_normal())),
+              ("white", 0.5)] for _ in range(chains)]
+    ds = ctx.dataset(x, y)
+    st, ll, acc, info = ds.mh_run([gterms(t) for t in inits], ig, 0.05, z, u, formula=G.FORMULA_GPML)
+    assert info == 0
+    min_margin = 1.0
+    for c in range(chains):
+        so, lo, ao, rc = oracle.mh_run(x, y, inits[c], ig, 0.05, z[:, c, :], u[:, c], formula=1, evals_per_iter=2)
+        assert rc == 0
+        assert np.array_equal(acc[:, c], ao), f"chain {c}: accept/reject sequences differ"
+        assert np.allclose(st[:, c, :], so, rtol=1e-12, atol=0)
+        assert np.allclose(ll[:, c], lo, rtol=1e-10, atol=0)
+    assert 0 < acc.sum() < acc.size
+    ds.close()
+
+
+def test_reference_api_mirror_end_to_end(oracle):
+    """The drop-in surface: GaussianProcess.loglikelihood / Predict.fit / KernelParameters.sample with
+    the reference's signatures, as the docs use them (docs/src/main/tut/docs/prediction.md:27-58)."""
+    import gpb200 as gp
+    rng = np.random.default_rng(8)
+    xs = np.sort(rng.uniform(-10, 10, 30))
+    params = gp.GaussianProcess.Parameters(gp.MeanParameters.zero, [gp.KernelParameters.se(3.0, 5.5), gp.KernelParameters.white(0.5)])
+    K = oracle.build_cov(xs, SE_W, 1e-3)
+    ys = np.linalg.cholesky(K) @ rng.standard_normal(30)
+    observed = [gp.GaussianProcess.Data(gp.One(float(a)), float(b)) for a, b in zip(xs, ys)]
+    ll = gp.GaussianProcess.loglikelihood(observed, gp.Location.euclidean)
+    assert rel(ll(params), oracle.loglik(xs, ys, SE_W)["ll_ref"]) < LL_RTOL
+    assert rel(ll(params, formula=gp.FORMULA_GPML), oracle.loglik(xs, ys, SE_W)["ll_gpml"]) < LL_RTOL
+    fitted = gp.Predict.fit([gp.One(-1.0), gp.One(0.5)], observed, gp.Location.euclidean, params)
+    mo, vo, _ = oracle.predict(xs, ys, SE_W, np.array([-1.0, 0.5]))
+    assert fitted[0][0] == gp.One(-1.0)
+    assert fitted[0][1].mean == pytest.approx(mo[0], rel=1e-7, abs=1e-9)
+    assert fitted[1][1].sigma == pytest.approx(math.sqrt(vo[1]), rel=1e-7)
+    D = gp.GaussianProcess.distanceMatrix([d.x for d in observed], gp.Location.euclidean)
+    assert D.shape == (30, 30) and D[3, 7] == abs(xs[3] - xs[7])
+    Kc = gp.KernelFunction.buildCov([d.x for d in observed], gp.KernelFunction.apply(params.kernelParameters), gp.Location.euclidean)
+    assert np.allclose(Kc + 1e-3 * np.eye(30), K, rtol=1e-15, atol=1e-15)
+    # one MH step function, host closures for prior / proposal as in SimulatedGp.scala:115-151
+    step = gp.KernelParameters.sample(observed, gp.Location.euclidean, lambda ks: 0.0,
+                                      lambda ks, r: [k.map(lambda v: v * math.exp(r.normal(0, 0.05))) for k in ks])
+    p = params
+    for _ in range(5):
+        p = step(p, rng)
+    assert isinstance(p, gp.GaussianProcess.Parameters) and len(p.toList()) == 3
+    with pytest.raises(gp.NotConvergedException):  # a bad proposal raises
+        ll(gp.GaussianProcess.Parameters(gp.MeanParameters.zero, [gp.KernelParameters.se(1.0, 50.0), gp.KernelParameters.white(-2.0)]))
+    assert np.allclose(gp.Predict.forwardSolve(np.linalg.cholesky(K), ys), sl.solve_triangular(np.linalg.cholesky(K), ys, lower=True), rtol=1e-11)
+    assert np.allclose(gp.Mcmc.backSolve(np.linalg.cholesky(K).T, ys), sl.solve_triangular(np.linalg.cholesky(K).T, ys), rtol=1e-11)
+
+
+# ---- BASELINE.json full sizes: properties + LAPACK twin (the oracle would take minutes) ------------
+def test_full_size_c2_n4096(ctx, oracle):
+    """configs[1]: single GP log-marginal-likelihood + predictive, n=4096, 2-D, SE+noise."""
+    from gpb200 import _lib as G
+    n = 4096
+    rng = np.random.default_rng(2)
+    x = rng.uniform(-10, 10, size=(n, 2))
+    K = oracle.build_cov(x, SE_W, 1e-3)
+    L = np.linalg.cholesky(K)
+    y = L @ rng.standard_normal(n)
+    ds = ctx.dataset(x, y)
+    r = ds.loglik_batch([gterms(SE_W)])[0]
+    u = sl.solve_triangular(L, y, lower=True)
+    S, C = np.log(np.diag(L)).sum(), n * 0.5 * math.log(2 * math.pi)
+    print("cond(K) ~", float(np.linalg.cond(K)))
+    assert r.info == 0
+    assert rel(G.ll_value(r, 1), -0.5 * u @ u - S - C) < LL_RTOL
+    assert rel(G.ll_value(r, 0), -0.5 * u @ u + 0.5 * (S + C) * u.sum()) < LL_RTOL
+    # factor property through the matrix-level entry point: L L^T reproduces K
+    Lg, info = ctx.potrf(K)
+    assert info == 0
+    assert np.abs(Lg @ Lg.T - K).max() < 1e-11 * np.abs(K).max() * 64
+    # predictive round trip: at the training locations the posterior mean solves K a = y
+    xs = rng.uniform(-10, 10, size=(512, 2))
+    mean, var, info = ds.predict(gterms(SE_W), xs, nugget=1e-6)
+    K6 = K + (1e-6 - 1e-3) * np.eye(n)
+    d = np.sqrt(((x[:, None, :] - xs[None, :, :]) ** 2).sum(-1))
+    Ks = 3.0 * np.exp(-(d * d) / 30.25)
+    cf = sl.cho_factor(K6, lower=True)
+    assert np.allclose(mean, Ks.T @ sl.cho_solve(cf, y), rtol=1e-6, atol=1e-7)
+    assert np.allclose(var, 3.5 - np.einsum("ij,ij->j", Ks, sl.cho_solve(cf, Ks)), rtol=1e-6, atol=1e-7)
+    ds.close()
+
+
+def test_full_size_c3_batch_of_chains_n1024(ctx, oracle):
+    """configs[2]: 256 independent proposals x n=1024 in one pass; spot-check against the oracle and
+    check every proposal against the linearity property Q(c*y) = c^2 Q(y)."""
+    from gpb200 import _lib as G
+    n, B = 1024, 256
+    x, y, _ = synth(oracle, n, 2, SE_W, 3)
+    rng = np.random.default_rng(4)
+    props = [[("se", 3.0 * math.exp(0.05 * rng.standard_normal()), 5.5 * math.exp(0.05 * rng.standard_normal())),
+              ("white", 0.5 * math.exp(0.05 * rng.standard_normal()))] for _ in range(B)]
+    ds = ctx.dataset(x, y)
+    rs = ds.loglik_batch([gterms(p) for p in props])
+    ds2 = ctx.dataset(x, 2.0 * y)
+    rs2 = ds2.loglik_batch([gterms(p) for p in props])
+    for b in range(B):
+        assert rs[b].info == 0
+        assert rel(rs2[b].Q, 4.0 * rs[b].Q) < 1e-13 and rs2[b].S == rs[b].S
+    for b in (0, 97, 255):
+        ro = oracle.loglik(x, y, props[b])
+        assert rel(G.ll_value(rs[b], 0), ro["ll_ref"]) < LL_RTOL and rel(G.ll_value(rs[b], 1), ro["ll_gpml"]) < LL_RTOL
+    ds.close(); ds2.close()
+
+
+def test_full_size_c5_sum_of_kernels_n8192(ctx, oracle):
+    """configs[4] shape (SE + SE + white, n=8192), one proposal: LAPACK twin on the host."""
+    from gpb200 import _lib as G
+    n = 8192
+    rng = np.random.default_rng(5)
+    x = rng.uniform(-15, 15, size=(n, 2))
+    d2 = ((x[:, None, :] - x[None, :, :]) ** 2).sum(-1)
+    d = np.sqrt(d2)
+    K = 3.0 * np.exp(-(d * d) / (5.5 * 5.5)) + 1.0 * np.exp(-(d * d) / (0.8 * 0.8)) + np.where(d == 0, 0.5, 0.0) + 1e-3 * np.eye(n)
+    L = np.linalg.cholesky(K)
+    y = L @ rng.standard_normal(n)
+    ds = ctx.dataset(x, y)
+    r = ds.loglik_batch([gterms(SE_SE_W)])[0]
+    u = sl.solve_triangular(L, y, lower=True)
+    S, C = np.log(np.diag(L)).sum(), n * 0.5 * math.log(2 * math.pi)
+    assert r.info == 0 and rel(G.ll_value(r, 1), -0.5 * u @ u - S - C) < LL_RTOL
+    ds.close()

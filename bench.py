@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py -- GP log-marginal-likelihood evaluations/s at n=4096 (BASELINE.json configs[1]) on
+N B200s, through libgpb200.so's C ABI.  Prints ONE JSON line (rank 0).
+
+  step      = one gpb_loglik_batch call: --batch fresh proposals (new hyper-parameters every step,
+              K is rebuilt and refactored every time; nothing is cached) on the resident dataset.
+  value     = evals/s from the device time of the step's kernels (CUDA events on the library's own
+              launching stream: build + factor/solve + epilogue), max over ranks.
+  e2e       = evals/s through the reference-facing call with HOST buffers: hyper-parameters go H2D
+              and the (Q, U1, S, info) results come D2H inside the timed region, every step.
+  roofline  = the factorisation kernel (k_chol_tasks): algorithmic FP64 flops / its average launch
+              duration vs the measured DMMA issue peak of this pool's B200 (37.1 TFLOP/s,
+              profiles/r01_dmma_shapes_microbench.log; MEASURED_PEAKS.json has no FP64 entry).
+  N > 1     : proposals are sharded across ranks (independent, no data-path collective); each rank
+              then all-gathers its log-likelihoods over NCCL (north_star: gather only). scaling=weak.
+  --impl reference : the CPU oracle (port of the Scala/Breeze path; the JVM is not in this image)
+              on all host cores, one independent evaluation per thread, same config and metric.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "gaussian-processes_b200"))
+
+N_TRAIN = 4096
+DIM = 2
+SEED = 2
+TRUE_TERMS = [("se", 3.0, 5.5), ("white", 0.5)]  # SimulatedGp.scala:30-33
+FP64_PEAK_TFLOPS = 37.1                          # measured DMMA.8x8x4 issue peak, B200 @1965 MHz
+METRIC = "gp_loglik_evals_per_sec_n4096"
+
+
+def chol_flops(n):
+    return n ** 3 / 3.0 + n ** 2 / 2.0 + n / 6.0 + float(n) ** 2  # dpotrf + one forward solve
+
+
+def make_dataset():
+    """n=4096, 2-D U(-10,10)^2, y = L z with the true kernel, seed 2."""
+    import scipy.linalg as sl
+    rng = np.random.default_rng(SEED)
+    x = rng.uniform(-10, 10, size=(N_TRAIN, DIM))
+    d2 = ((x[:, None, :] - x[None, :, :]) ** 2).sum(-1)
+    K = 3.0 * np.exp(-d2 / (5.5 * 5.5)) + (0.5 + 1e-3) * np.eye(N_TRAIN)
+    y = sl.cholesky(K, lower=True) @ rng.standard_normal(N_TRAIN)
+    return x, y
+
+
+def proposals(rng, batch):
+    """Fresh hyper-parameters around the truth (log-normal jitter 0.05, as the example proposal)."""
+    out = []
+    for _ in range(batch):
+        z = rng.standard_normal(3) * 0.05
+        out.append([("se", 3.0 * math.exp(z[0]), 5.5 * math.exp(z[1])), ("white", 0.5 * math.exp(z[2]))])
+    return out
+
+
+def gterms(terms):
+    return [(0, t[1], t[2]) if t[0] == "se" else (1, t[1], 0.0) for t in terms]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_evals(x, y, term_lists, threads):
+    """Oracle (test infrastructure; here only as the timed CPU baseline): one independent n=4096
+    evaluation per host thread, each single-threaded like the reference's F2J path."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as o
+    o.lib()
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        res = list(ex.map(lambda t: o.loglik(x, y, t, nugget=1e-3), term_lists))
+    dt = time.perf_counter() - t0
+    assert all(r["info"] == 0 for r in res)
+    return len(term_lists) / dt, dt, res
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path restated (oracle port; JVM unavailable on this
+    box), all host cores, same config / metric / unit.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    x, y = make_dataset()
+    rng = np.random.default_rng(1234)
+    for _ in range(args.warmup):
+        cpu_evals(x, y, proposals(rng, cores), cores)
+    total_t, total_n = 0.0, 0
+    for _ in range(args.steps):
+        _, dt, _ = cpu_evals(x, y, proposals(rng, cores), cores)
+        total_t += dt; total_n += cores
+    v = total_n / total_t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "evals/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"C2: n={N_TRAIN} 2-D SE+white log-marginal-likelihood, {cores} independent proposals per step (one per host thread)"},
+        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} steps x {cores} full n={N_TRAIN} evaluations, 1 thread each (reference JVM path: unavailable on this box)"},
+        "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    from gpb200 import _lib as G
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- gpb200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    ctx = G.Context(local)
+    x, y = make_dataset()
+    ds = ctx.dataset(x, y)
+    B = args.batch
+    rng = np.random.default_rng(1000 + rank)
+    gather_in = torch.zeros(B, dtype=torch.float64, device=f"cuda:{local}")
+    gather_out = torch.zeros(B * world, dtype=torch.float64, device=f"cuda:{local}") if world > 1 else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        props = [gterms(p) for p in proposals(rng, B)]
+        rs = ds.loglik_batch(props, nugget=1e-3)       # H2D params, kernels, D2H results
+        t = ctx.last_timing()
+        if dist is not None:                            # gather the log-likelihoods (north_star)
+            gather_in.copy_(torch.tensor([G.ll_value(r, 0) for r in rs], dtype=torch.float64))
+            dist.all_gather_into_tensor(gather_out, gather_in)
+        return rs, t
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    l0 = ctx.launch_count()
+    dev_ms, chol_ms = 0.0, 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        rs, t = step()
+        dev_ms += t[0] + t[1] + t[2]
+        chol_ms += t[1]
+        assert all(r.info == 0 for r in rs)
+    barrier()
+    wall = time.perf_counter() - t0
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop()
+
+    # max over ranks of both clocks
+    tt = torch.tensor([dev_ms, wall, chol_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dev_ms, wall, chol_ms = (float(v) for v in tt.cpu())
+    evals = args.steps * B * world
+    value = evals / (dev_ms * 1e-3)
+    e2e = evals / wall
+    achieved = args.steps * B * chol_flops(N_TRAIN) / (chol_ms * 1e-3) * 1e-12
+
+    extra = {}
+    if rank == 0 and world == 1 and not args.no_extras:
+        extra = extras(ctx, ds, G, x, y)
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            v, dt, res = cpu_evals(x, y, proposals(np.random.default_rng(7), cores), cores)
+            cpu = {"value": v, "unit": "evals/s", "cores": cores, "kind": "port",
+                   "sample": f"{cores} full n={N_TRAIN} evaluations, one per thread, {dt:.1f} s (reference JVM path: unavailable on this box)"}
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "chol_traffic_bytes_per_launch.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(str(B))
+        line = {
+            "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C2: n={N_TRAIN} 2-D SE+white log-marginal-likelihood, batch of {B} independent proposals per step per GPU",
+                       "batch": B, "n": N_TRAIN, "dim": DIM, "parallelism": f"proposal-sharded x{world}",
+                       "l2": "inputs larger than L2 (each proposal rebuilds and refactors its own 134 MB matrix)"},
+            "e2e": {"value": e2e, "unit": "evals/s", "h2d_bytes_per_step": B * 192,
+                    "d2h_bytes_per_step": B * 40 + 8},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "k_chol_tasks", "achieved": achieved,
+                         "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": achieved / FP64_PEAK_TFLOPS,
+                         "traffic": traffic,
+                         "peak_source": "measured FP64 DMMA issue peak on this pool (profiles/r01_dmma_shapes_microbench.log); MEASURED_PEAKS.json has no FP64 entry; cuBLAS DGEMM reaches 35.4"},
+            "cpu_baseline": cpu,
+            "extra": extra,
+        }
+        print(json.dumps(line), flush=True)
+    ds.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def extras(ctx, ds, G, x, y):
+    """Secondary numbers named by BASELINE.json's metric string (not the headline line)."""
+    out = {}
+    rng = np.random.default_rng(5)
+    # latency mode: one proposal at a time (what a single MH chain sees)
+    for _ in range(3):
+        ds.loglik_batch([gterms(proposals(rng, 1)[0])])
+    t0 = time.perf_counter(); dev = 0.0
+    for _ in range(20):
+        ds.loglik_batch([gterms(proposals(rng, 1)[0])]); dev += sum(ctx.last_timing())
+    out["single_proposal_evals_per_sec_e2e"] = 20 / (time.perf_counter() - t0)
+    out["single_proposal_evals_per_sec_device"] = 20 / (dev * 1e-3)
+    # C3: 256 MH chains x n=1024 on this GPU
+    n, chains, iters = 1024, 256, 10
+    r2 = np.random.default_rng(3)
+    x3 = r2.uniform(-10, 10, size=(n, 2))
+    d2 = ((x3[:, None, :] - x3[None, :, :]) ** 2).sum(-1)
+    K = 3.0 * np.exp(-d2 / 30.25) + 0.501 * np.eye(n)
+    y3 = np.linalg.cholesky(K) @ r2.standard_normal(n)
+    ds3 = ctx.dataset(x3, y3)
+    ig = [[3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]
+    inits = [gterms(p) for p in proposals(r2, chains)]
+    z, u = G.philox_streams(9, 0, chains, iters, 3)
+    ds3.mh_run(inits, ig, 0.05, z[:2], u[:2], on_notpd=1)
+    t0 = time.perf_counter()
+    st, ll, acc, info = ds3.mh_run(inits, ig, 0.05, z, u, on_notpd=1)
+    dt = time.perf_counter() - t0
+    out["mcmc_iters_per_sec_256chains_n1024_1gpu"] = iters / dt
+    out["mcmc_accept_rate"] = float(acc.mean())
+    ds3.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        args.steps = 3 if args.steps is None else args.steps
+        args.warmup = 1 if args.warmup is None else args.warmup
+        run_reference(args)
+    else:
+        args.steps = 20 if args.steps is None else args.steps
+        args.warmup = 3 if args.warmup is None else args.warmup
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

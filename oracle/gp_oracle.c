@@ -132,21 +132,34 @@ static int potf2_lower(int n, double *a, int lda) {
   return 0;
 }
 
+
+/* y[0..m) += sum_{l<k} (-w[l*ldw]) * a[l*lda + 0..m), applied in ascending l per element. */
+static void axpy_cols(int m, int k, const double *w, int ldw, const double *a, int lda, double *y) {
+  int l = 0;
+  for (; l + 4 <= k; l += 4) {
+    const double t0 = -w[(size_t)l * ldw], t1 = -w[(size_t)(l + 1) * ldw];
+    const double t2 = -w[(size_t)(l + 2) * ldw], t3 = -w[(size_t)(l + 3) * ldw];
+    const double *a0 = a + (size_t)l * lda, *a1 = a0 + lda, *a2 = a1 + lda, *a3 = a2 + lda;
+    for (int i = 0; i < m; ++i) y[i] = (((y[i] + t0 * a0[i]) + t1 * a1[i]) + t2 * a2[i]) + t3 * a3[i];
+  }
+  for (; l < k; ++l) {
+    const double t0 = -w[(size_t)l * ldw];
+    const double *a0 = a + (size_t)l * lda;
+    for (int i = 0; i < m; ++i) y[i] += t0 * a0[i];
+  }
+}
+
 /* dpotrf 'L', NB = 64 (ilaenv default for DPOTRF). */
 int orc_potrf_lower(int n, double *a, int lda) {
   const int nb = 64;
   if (nb >= n) return potf2_lower(n, a, lda);
   for (int j = 0; j < n; j += nb) {
     int jb = n - j < nb ? n - j : nb;
-    /* dsyrk('L','N', jb, j, -1, A(j,0), lda, 1, A(j,j), lda) */
+    /* dsyrk('L','N', jb, j, -1, A(j,0), lda, 1, A(j,j), lda): C(i,c) += -A(c,l) * A(i,l), l ascending.
+     * The l loop is unrolled-and-jammed by 4 (fewer passes over the C column); every element
+     * still receives its updates in ascending l, so results equal the reference BLAS loop nest. */
     for (int c = 0; c < jb; ++c)
-      for (int l = 0; l < j; ++l) {
-        double v = A_(j + c, l);
-        if (v != 0.0) {
-          double temp = -v;
-          for (int i = c; i < jb; ++i) A_(j + i, j + c) += temp * A_(j + i, l);
-        }
-      }
+      axpy_cols(jb - c, j, &A_(j + c, 0), lda, &A_(j + c, 0), lda, &A_(j + c, j + c));
     int info = potf2_lower(jb, &A_(j, j), lda);
     if (info != 0) return info + j;
     if (j + jb < n) {
@@ -154,15 +167,7 @@ int orc_potrf_lower(int n, double *a, int lda) {
       double *b = &A_(j + jb, j);
       /* dgemm('N','T', m, jb, j, -1, A(j+jb,0), lda, A(j,0), lda, 1, A(j+jb,j), lda) */
       for (int c = 0; c < jb; ++c)
-        for (int l = 0; l < j; ++l) {
-          double v = A_(j + c, l);
-          if (v != 0.0) {
-            double temp = -v;
-            const double *al = &A_(j + jb, l);
-            double *bc = b + (size_t)c * lda;
-            for (int i = 0; i < m; ++i) bc[i] += temp * al[i];
-          }
-        }
+        axpy_cols(m, j, &A_(j + c, 0), lda, &A_(j + jb, 0), lda, b + (size_t)c * lda);
       /* dtrsm('R','L','T','N', m, jb, 1, A(j,j), lda, A(j+jb,j), lda) */
       for (int k = 0; k < jb; ++k) {
         double temp = 1.0 / A_(j + k, j + k);

@@ -66,9 +66,20 @@ int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y
   launch_build(ctx->stream, g, d_x, d_y, d_xstar, ctx->hyper, nugget, ctx->mats, 0, 0);
   ctx->launches += 1;
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-  ctx->launches += launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info,
-                               ctx->sched, ctx->sched_mode, ctx->num_sms);
+  int rc = do_chol(ctx, g, 0);
+  if (rc) return rc;
   CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+  return GPB_OK;
+}
+
+int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
+  const int nl = launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
+                             ctx->sched_mode, ctx->num_sms, solve_only);
+  if (nl < 0) {
+    ctx->cuda_err = "cuTensorMapEncodeTiled failed (TMA descriptor of the workspace)";
+    return GPB_E_CUDA;
+  }
+  ctx->launches += nl;
   return GPB_OK;
 }
 
@@ -298,8 +309,8 @@ int gpb_potrf(gpb_ctx* ctx, int n, double* A, int* info) {
   launch_pad_identity(ctx->stream, g, ctx->mats);
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-  ctx->launches += 1 + launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info,
-                                   ctx->sched, ctx->sched_mode, ctx->num_sms);
+  ctx->launches += 1;
+  if ((rc = do_chol(ctx, g, 0))) return rc;
   CK(cudaEventRecord(ctx->ev[2], ctx->stream));
   launch_zero_upper(ctx->stream, g, ctx->mats);
   ctx->launches += 1;

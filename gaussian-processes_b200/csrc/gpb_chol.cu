@@ -21,6 +21,8 @@
 //
 // Roofline: trailing contraction n^3/3 flop on the FP64 tensor pipe (37.1 TFLOP/s measured DMMA
 // issue peak on this B200, profiles/r01_dmma_shapes_microbench.log).
+#include <cuda.h>
+
 #include "gpb_internal.h"
 
 namespace gpb {
@@ -30,10 +32,10 @@ constexpr int STAGES = 4;
 constexpr int NCONS = 128;             // consumer threads: 4 warps, 32x32 sub-tile each
 constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
 constexpr int STAGE_DOUBLES = 2 * KC * LDT;
-constexpr uint32_t STAGE_TX_BYTES = 2 * KC * TILE * sizeof(double);
+constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 
-struct __align__(16) CholSmem {
+struct __align__(128) CholSmem {
   double stage[STAGES][STAGE_DOUBLES];  // [0..KC) panel j ("c" rows), [KC..2KC) panel i ("r" rows)
   double Cs[TILE * LDT];                // C tile, column-major [c][r]
   double Ls[TILE * LDT];                // L_jj^-T tile, column-major [c][k]
@@ -136,14 +138,15 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
+k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
              int static_sched, int solve_only) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
+    tma_prefetch_desc(&tmap);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], 1); }
     mbar_fence_init();
@@ -174,30 +177,26 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
       if (t < 0) break;
       const TaskDesc d = decode_task(g, t, jcache);
       if (solve_only && d.i < g.nt) continue;  // L is given: no accumulation for top-square tiles
-      const double* M = mats + (size_t)d.b * g.mat_stride;
       const int* done_b = done + (size_t)d.b * g.rt;
-      // lanes 0..15 fetch panel j rows (c operand), lanes 16..31 panel i rows (r operand)
-      const int rowbase = (lane < KC ? d.j : d.i) * TILE;
-      for (int kc = 0; kc < d.j; ++kc) {
-        if (lane == 0) {
+      if (lane == 0) {
+        // one elected lane drives the ring: two TMA boxes per stage ({LDT rows x KC cols}: the
+        // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
+        for (int kc = 0; kc < d.j; ++kc) {
           wait_counter(done_b + d.i, kc + 1, &sched->error);
           wait_counter(done_b + d.j, kc + 1, &sched->error);
-        }
-        __syncwarp();
-        fence_proxy_async();
+          fence_proxy_async();
 #pragma unroll 1
-        for (int s = 0; s < TILE / KC; ++s) {
-          if (lane == 0) {
+          for (int s = 0; s < TILE / KC; ++s) {
             if (!mbar_wait(&sm.empty[stage], phase ^ 1)) atomicExch(&sched->error, 3);
             mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+            const int col = kc * TILE + s * KC;
+            tma_load_3d(&sm.stage[stage][0], &tmap, d.j * TILE, col, d.b, &sm.full[stage]);
+            tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col, d.b, &sm.full[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          __syncwarp();
-          const int col = kc * TILE + s * KC + (lane & (KC - 1));
-          bulk_g2s(&sm.stage[stage][lane * LDT], M + (size_t)col * g.ld + rowbase,
-                   TILE * sizeof(double), &sm.full[stage]);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
+      __syncwarp();
     }
     return;
   }
@@ -333,14 +332,34 @@ k_chol_tasks(Geom g, double* __restrict__ mats, double* __restrict__ linvt, int*
   }
 }
 
+static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                               const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                               CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                               CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || !fn)
+      return false;
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  const cuuint64_t dims[3] = {(cuuint64_t)g.ld, (cuuint64_t)g.npad, (cuuint64_t)g.batch};
+  const cuuint64_t strides[2] = {(cuuint64_t)g.ld * sizeof(double), (cuuint64_t)g.mat_stride * sizeof(double)};
+  const cuuint32_t box[3] = {(cuuint32_t)LDT, (cuuint32_t)KC, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, mats, dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done, int* info,
                 SchedState* sched, int mode, int num_sms, int solve_only) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)sizeof(CholSmem));
-    attr_set = true;
-  }
+  cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+  CUtensorMap tmap;
+  if (!make_tmap(&tmap, g, mats)) return -1;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
   cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
   cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
@@ -348,7 +367,7 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
   int launches = 0;
   if (mode == 0) {
     int grid = (int)(total < num_sms ? total : num_sms);
-    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched, 0,
+    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched, 0,
                                                            (int)total, 0, solve_only);
     launches = 1;
   } else {
@@ -356,13 +375,13 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
     for (int j = 0; j < g.nt; ++j) {
       long long ndiag = g.batch, noff = (long long)g.batch * (g.rt - j - 1);
       int grid = (int)(ndiag < num_sms ? ndiag : num_sms);
-      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
+      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
                                                              (int)begin, (int)(begin + ndiag), 1, solve_only);
       begin += ndiag;
       ++launches;
       if (noff > 0) {
         grid = (int)(noff < 2LL * num_sms ? noff : 2LL * num_sms);
-        k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(g, mats, linvt, done, info, sched,
+        k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
                                                                (int)begin, (int)(begin + noff), 1, solve_only);
         begin += noff;
         ++launches;

@@ -80,5 +80,7 @@ int fill_hyper(Hyper* h, const gpb_term* terms, int nterms, const double* beta, 
 int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y,
                const double* d_xstar, double nugget);
 int finish_timing(gpb_ctx* ctx);
+// Launch the factorisation / panel-solve kernel(s) on ctx->stream; counts launches; status out.
+int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only);
 
 }  // namespace gpbh

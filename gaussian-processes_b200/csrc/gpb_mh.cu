@@ -154,8 +154,8 @@ int trsm_common(gpb_ctx* ctx, int n, int nrhs, const double* T, double* B, int r
   k_pack_rhs<<<dim3((g.apad + 63) / 64, g.npad), 64, 0, ctx->stream>>>(g, dB, nrhs, reverse, ctx->mats);
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-  ctx->launches += 2 + launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info,
-                                   ctx->sched, ctx->sched_mode, ctx->num_sms, /*solve_only=*/1);
+  ctx->launches += 2;
+  if ((rc = do_chol(ctx, g, /*solve_only=*/1))) return rc;
   CK(cudaEventRecord(ctx->ev[2], ctx->stream));
   k_unpack_rhs<<<dim3((nrhs + 63) / 64, n), 64, 0, ctx->stream>>>(g, ctx->mats, nrhs, reverse, dB);
   ctx->launches += 1;
@@ -285,8 +285,8 @@ int gpb_mh_run(gpb_ctx* ctx, const gpb_dataset* ds, int chains, int iters, const
   for (int it = -1; it < iters; ++it) {
     k_mh_propose<<<gb, tb, 0, st>>>(md, it, d_cur, d_z, d_prop, ctx->hyper);
     launch_build(st, g, ds->x, ds->y, nullptr, ctx->hyper, opts->nugget, ctx->mats, 0, 0);
-    ctx->launches += 2 + launch_chol(st, g, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
-                                     ctx->sched_mode, ctx->num_sms);
+    ctx->launches += 2;
+    if ((rc = do_chol(ctx, g, 0))) return rc;
     launch_ll_epilogue(st, g, ctx->mats, ctx->info, ctx->ll);
     k_mh_accept<<<gb, tb, 0, st>>>(md, it, ctx->ll, d_prop, d_uu, d_cur, d_curll, d_states, d_outll,
                                    d_acc, d_bad);

@@ -50,22 +50,30 @@ size_t chol_smem_bytes() { return sizeof(CholSmem); }
 
 struct TaskDesc { int b, i, j; };
 
-// tasks before block column j:  batch * sum_{j'<j} (rt - j')
-__device__ __forceinline__ long long col_start(const Geom& g, int j) {
-  return (long long)g.batch * ((long long)j * g.rt - (long long)j * (j - 1) / 2);
+// Ticket order (topological; chosen so the next diagonal block is factored while the bulk of the
+// current block column is still being solved):
+//   group -1 : diag(0,0) of every proposal
+//   group  j : A  (j+1, j)      the tile the next diagonal block depends on      [if j+1 < rt]
+//              B  diag(j+1,j+1)                                                  [if j+1 < nt]
+//              C  (i, j), i >= j+2
+// tickets before group j (j <= nt-1):  batch * (1 + j*rt - j(j+1)/2 + j)
+__device__ __host__ __forceinline__ long long group_start(const Geom& g, int j) {
+  return (long long)g.batch * (1 + (long long)j * g.rt - (long long)j * (j + 1) / 2 + j);
 }
 __device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcache) {
-  while (jcache + 1 < g.nt && (long long)t >= col_start(g, jcache + 1)) ++jcache;
-  while (jcache > 0 && (long long)t < col_start(g, jcache)) --jcache;
   TaskDesc d;
-  d.j = jcache;
-  int local = t - (int)col_start(g, jcache);
-  if (local < g.batch) {
-    d.b = local; d.i = d.j;
-  } else {
-    int l2 = local - g.batch, per = g.rt - d.j - 1;
-    d.b = l2 / per; d.i = d.j + 1 + l2 % per;
-  }
+  if (t < g.batch) { d.b = t; d.i = 0; d.j = 0; return d; }
+  while (jcache + 1 < g.nt && (long long)t >= group_start(g, jcache + 1)) ++jcache;
+  while (jcache > 0 && (long long)t < group_start(g, jcache)) --jcache;
+  const int j = jcache;
+  int local = t - (int)group_start(g, j);
+  const int nA = (j + 1 < g.rt) ? g.batch : 0, nB = (j + 1 < g.nt) ? g.batch : 0;
+  if (local < nA) { d.b = local; d.i = j + 1; d.j = j; return d; }
+  local -= nA;
+  if (local < nB) { d.b = local; d.i = j + 1; d.j = j + 1; return d; }
+  local -= nB;
+  const int per = g.rt - j - 2;
+  d.b = local / per; d.i = j + 2 + local % per; d.j = j;
   return d;
 }
 
@@ -371,21 +379,20 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
                                                            (int)total, 0, solve_only);
     launches = 1;
   } else {
-    long long begin = 0;
-    for (int j = 0; j < g.nt; ++j) {
-      long long ndiag = g.batch, noff = (long long)g.batch * (g.rt - j - 1);
-      int grid = (int)(ndiag < num_sms ? ndiag : num_sms);
+    // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
+    auto run = [&](long long begin, long long count) {
+      if (count <= 0) return;
+      int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
       k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
-                                                             (int)begin, (int)(begin + ndiag), 1, solve_only);
-      begin += ndiag;
+                                                             (int)begin, (int)(begin + count), 1, solve_only);
       ++launches;
-      if (noff > 0) {
-        grid = (int)(noff < 2LL * num_sms ? noff : 2LL * num_sms);
-        k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
-                                                               (int)begin, (int)(begin + noff), 1, solve_only);
-        begin += noff;
-        ++launches;
-      }
+    };
+    run(0, g.batch);
+    for (int j = 0; j < g.nt; ++j) {
+      long long begin = group_start(g, j);
+      const long long nA = (j + 1 < g.rt) ? g.batch : 0, nB = (j + 1 < g.nt) ? g.batch : 0;
+      const long long nC = (long long)g.batch * (g.rt - j - 2 > 0 ? g.rt - j - 2 : 0);
+      run(begin, nA); run(begin + nA, nB); run(begin + nA + nB, nC);
     }
   }
   return launches;

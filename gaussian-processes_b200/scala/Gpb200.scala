@@ -1,0 +1,137 @@
+// Gpb200.scala -- reference-side binding of libgpb200.so (include/gpb200.h) through the Java
+// Foreign Function & Memory API (Panama, JDK 22+; no C glue).  SOURCE ONLY: this image has no
+// JVM/scalac, so this file is not compiled or tested here (DESIGN.md section 1).  It shows how the
+// reference's public methods keep their signatures while the hot path runs on the B200.
+//
+// Drop-in points (core/src/main/scala/gp/):
+//   GaussianProcess.loglikelihood  GaussianProcess.scala:109-127  -> Gpb200.loglikelihood
+//   Predict.fit                    Predict.scala:57-94            -> Gpb200.fit
+//   KernelParameters.sample        KernelParameters.scala:231-246 -> unchanged (it calls loglikelihood)
+package com.github.jonnylaw.gp
+
+import java.lang.foreign._
+import java.lang.foreign.ValueLayout._
+import java.lang.invoke.MethodHandle
+import breeze.stats.distributions.Gaussian
+import GaussianProcess.{Data, Parameters}
+
+object Gpb200 {
+  private val linker = Linker.nativeLinker()
+  private val lib = SymbolLookup.libraryLookup("libgpb200.so", Arena.global())
+  private def fn(name: String, fd: FunctionDescriptor): MethodHandle =
+    linker.downcallHandle(lib.find(name).orElseThrow(), fd)
+
+  // struct gpb_term { int kind; double p0, p1, p2; }   (32 bytes, 8-aligned)
+  private val TERM = MemoryLayout.structLayout(JAVA_INT.withName("kind"), MemoryLayout.paddingLayout(4),
+    JAVA_DOUBLE.withName("p0"), JAVA_DOUBLE.withName("p1"), JAVA_DOUBLE.withName("p2"))
+  // struct gpb_ll { double Q, U1, S; int n; int info; } (32 bytes)
+  private val LL = MemoryLayout.structLayout(JAVA_DOUBLE.withName("Q"), JAVA_DOUBLE.withName("U1"),
+    JAVA_DOUBLE.withName("S"), JAVA_INT.withName("n"), JAVA_INT.withName("info"))
+
+  private val ctxCreate = fn("gpb_ctx_create", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS))
+  private val dsCreate = fn("gpb_dataset_create",
+    FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS))
+  private val dsDestroy = fn("gpb_dataset_destroy", FunctionDescriptor.ofVoid(ADDRESS))
+  private val loglik = fn("gpb_loglik", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+    JAVA_INT, ADDRESS, JAVA_INT, JAVA_DOUBLE, ADDRESS))
+  private val llValue = fn("gpb_ll_value", FunctionDescriptor.of(JAVA_DOUBLE, ADDRESS, JAVA_INT))
+  private val predict = fn("gpb_predict", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+    JAVA_INT, JAVA_DOUBLE, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS))
+
+  // one context per JVM thread (a gpb_ctx is not shared between threads: SimulatedGp.scala:163-165
+  // runs 2 chains on 2 threads)
+  private val ctx = new ThreadLocal[MemorySegment] {
+    override def initialValue(): MemorySegment = {
+      val out = Arena.global().allocate(ADDRESS)
+      check(ctxCreate.invoke(0, out).asInstanceOf[Int])
+      out.get(ADDRESS, 0)
+    }
+  }
+
+  private def check(status: Int): Unit =
+    if (status != 0) throw new RuntimeException(s"gpb200 status $status") // no CPU fallback
+
+  private def requireEuclidean(dist: (Location[Double], Location[Double]) => Double): Unit = {
+    // dist is an arbitrary closure in the reference; only Location.euclidean ships (SURVEY 0.2m):
+    // probe it on a few pairs and refuse anything else instead of falling back to the CPU.
+    val probes = Vector((One(0.0), One(3.0)), (One(-1.5), One(2.25)))
+    if (!probes.forall { case (a, b) => dist(a, b) == Location.euclidean(a, b) })
+      throw new UnsupportedOperationException("gpb200 supports Location.euclidean only")
+  }
+
+  private def soa(xs: Vector[Location[Double]], arena: Arena): (MemorySegment, Int) = {
+    val dim = xs.head.toVector.size
+    val seg = arena.allocate(JAVA_DOUBLE, xs.size.toLong * dim)
+    for ((x, i) <- xs.zipWithIndex; (v, d) <- x.toVector.zipWithIndex)
+      seg.setAtIndex(JAVA_DOUBLE, d.toLong * xs.size + i, v)
+    (seg, dim)
+  }
+
+  private def terms(ps: Vector[KernelParameters], arena: Arena): MemorySegment = {
+    val seg = arena.allocate(TERM, ps.size)
+    ps.zipWithIndex.foreach { case (p, i) =>
+      val (kind, p0, p1) = p match {
+        case SquaredExp(h, s) => (0, h, s)
+        case White(s)         => (1, s, 0.0)
+        case Matern(s, nu, _) => (2, s, nu) // -> GPB_E_UNSUPPORTED
+      }
+      val o = i * TERM.byteSize()
+      seg.set(JAVA_INT, o, kind); seg.set(JAVA_DOUBLE, o + 8, p0); seg.set(JAVA_DOUBLE, o + 16, p1)
+    }
+    seg
+  }
+
+  /** Same signature and currying as GaussianProcess.loglikelihood (GaussianProcess.scala:109-111):
+    * the observations are uploaded when the outer function is applied. */
+  def loglikelihood(observed: Vector[Data],
+                    dist: (Location[Double], Location[Double]) => Double): Parameters => Double = {
+    requireEuclidean(dist)
+    val arena = Arena.ofShared()
+    val (x, dim) = soa(observed.map(_.x), arena)
+    val y = arena.allocateFrom(JAVA_DOUBLE, observed.map(_.y): _*)
+    val dsOut = arena.allocate(ADDRESS)
+    check(dsCreate.invoke(ctx.get, observed.size, dim, x, y, dsOut).asInstanceOf[Int])
+    val ds = dsOut.get(ADDRESS, 0)
+
+    { p: Parameters =>
+      val a = Arena.ofConfined()
+      try {
+        val beta = p.meanParameters.toList
+        val out = a.allocate(LL)
+        check(loglik.invoke(ctx.get, ds, terms(p.kernelParameters, a), p.kernelParameters.size,
+          if (beta.isEmpty) MemorySegment.NULL else a.allocateFrom(JAVA_DOUBLE, beta: _*),
+          beta.size, 1e-3, out).asInstanceOf[Int])
+        if (out.get(JAVA_INT, 28) != 0) // breeze.linalg.cholesky throws on a non-PD matrix
+          throw new breeze.linalg.NotConvergedException(breeze.linalg.NotConvergedException.Divergence)
+        llValue.invoke(out, 0 /* GPB_FORMULA_AS_PARSED: what :126 computes */).asInstanceOf[Double]
+      } finally a.close()
+    }
+  }
+
+  /** Same signature as Predict.fit (Predict.scala:57-61). */
+  def fit(newXs: Vector[Location[Double]], observed: Vector[Data],
+          dist: (Location[Double], Location[Double]) => Double,
+          p: Parameters): Vector[(Location[Double], Gaussian)] = {
+    requireEuclidean(dist)
+    val a = Arena.ofConfined()
+    try {
+      val (x, dim) = soa(observed.map(_.x), a)
+      val y = a.allocateFrom(JAVA_DOUBLE, observed.map(_.y): _*)
+      val dsOut = a.allocate(ADDRESS)
+      check(dsCreate.invoke(ctx.get, observed.size, dim, x, y, dsOut).asInstanceOf[Int])
+      val ds = dsOut.get(ADDRESS, 0)
+      val (xs, _) = soa(newXs, a)
+      val m = newXs.size
+      val mean = a.allocate(JAVA_DOUBLE, m); val vari = a.allocate(JAVA_DOUBLE, m)
+      val info = a.allocate(JAVA_INT)
+      check(predict.invoke(ctx.get, ds, terms(p.kernelParameters, a), p.kernelParameters.size, 1e-6, m,
+        xs, mean, vari, info).asInstanceOf[Int])
+      dsDestroy.invoke(ds)
+      if (info.get(JAVA_INT, 0) != 0)
+        throw new breeze.linalg.NotConvergedException(breeze.linalg.NotConvergedException.Divergence)
+      newXs.zipWithIndex.map { case (l, i) =>
+        (l, Gaussian(mean.getAtIndex(JAVA_DOUBLE, i), math.sqrt(vari.getAtIndex(JAVA_DOUBLE, i))))
+      }
+    } finally a.close()
+  }
+}

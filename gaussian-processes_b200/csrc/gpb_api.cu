@@ -73,8 +73,16 @@ int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y
 }
 
 int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
+  unsigned long long* trace = nullptr;
+  if (ctx->trace_on) {
+    ctx->trace_tasks = chol_task_count(g);
+    int rc = grow(ctx, &ctx->trace, &ctx->trace_n, (size_t)ctx->trace_tasks * CHOL_TRACE_SLOTS);
+    if (rc) return rc;
+    cudaMemsetAsync(ctx->trace, 0, sizeof(unsigned long long) * ctx->trace_tasks * CHOL_TRACE_SLOTS, ctx->stream);
+    trace = ctx->trace;
+  }
   const int nl = launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
-                             ctx->sched_mode, ctx->num_sms, solve_only);
+                             ctx->sched_mode, ctx->num_sms, solve_only, trace);
   if (nl < 0) {
     ctx->cuda_err = "cuTensorMapEncodeTiled failed (TMA descriptor of the workspace)";
     return GPB_E_CUDA;
@@ -125,6 +133,18 @@ int gpb_last_timing(const gpb_ctx* ctx, float* t3) {
   for (int i = 0; i < 3; ++i) t3[i] = ctx->timing[i];
   return GPB_OK;
 }
+int gpb_set_trace(gpb_ctx* ctx, int enable) {
+  if (!ctx) return GPB_E_INVALID;
+  ctx->trace_on = enable ? 1 : 0;
+  return GPB_OK;
+}
+long long gpb_get_trace(gpb_ctx* ctx, unsigned long long* out, long long max_tasks) {
+  if (!ctx || !ctx->trace) return 0;
+  long long nt = ctx->trace_tasks < max_tasks ? ctx->trace_tasks : max_tasks;
+  if (out && nt > 0)
+    cudaMemcpy(out, ctx->trace, sizeof(unsigned long long) * nt * CHOL_TRACE_SLOTS, cudaMemcpyDeviceToHost);
+  return ctx->trace_tasks;
+}
 int gpb_set_sched(gpb_ctx* ctx, int mode) {
   if (!ctx || mode < 0 || mode > 1) return GPB_E_INVALID;
   ctx->sched_mode = mode;
@@ -160,7 +180,7 @@ void gpb_ctx_destroy(gpb_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   cudaFree(ctx->mats); cudaFree(ctx->linvt); cudaFree(ctx->done); cudaFree(ctx->info);
-  cudaFree(ctx->hyper); cudaFree(ctx->ll); cudaFree(ctx->aux); cudaFree(ctx->sched);
+  cudaFree(ctx->trace); cudaFree(ctx->hyper); cudaFree(ctx->ll); cudaFree(ctx->aux); cudaFree(ctx->sched);
   cudaFreeHost(ctx->h_hyper); cudaFreeHost(ctx->h_ll); cudaFreeHost(ctx->h_sched);
   for (int i = 0; i < 4; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);

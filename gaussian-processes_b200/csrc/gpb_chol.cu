@@ -27,12 +27,23 @@
 
 namespace gpb {
 
-constexpr int KC = 16;                 // panel columns per pipeline stage
-constexpr int STAGES = 4;
+#ifndef GPB_KC
+#define GPB_KC 16
+#endif
+#ifndef GPB_STAGES
+#define GPB_STAGES 2
+#endif
+#ifndef GPB_CTAS_PER_SM
+#define GPB_CTAS_PER_SM 2
+#endif
+constexpr int KC = GPB_KC;             // panel columns per pipeline stage
+constexpr int STAGES = GPB_STAGES;
+constexpr int CTAS_PER_SM = GPB_CTAS_PER_SM;  // co-resident CTAs: one factors/solves while the other contracts
 constexpr int NCONS = 128;             // consumer threads: 4 warps, 32x32 sub-tile each
 constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
 constexpr int STAGE_DOUBLES = 2 * KC * LDT;
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
+constexpr int TRACE_SLOTS = 10;
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 
 struct __align__(128) CholSmem {
@@ -47,8 +58,26 @@ struct __align__(128) CholSmem {
 };
 
 size_t chol_smem_bytes() { return sizeof(CholSmem); }
+long long chol_task_count(const Geom& g) {
+  return (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
+}
 
 struct TaskDesc { int b, i, j; };
+
+// Optional per-task trace (debug builds of the schedule analysis; trace == nullptr in production):
+// [0] globaltimer at receipt, [1] clock at receipt, [2] first stage landed, [3] contraction done,
+// [4] dependency on the diagonal block satisfied, [5] factor / solve done, [6] clock at release,
+// [7] globaltimer at release, [8] SM id, [9] last chunk's first stage landed.
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long v;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
+  return v;
+}
+__device__ __forceinline__ unsigned int smid() {
+  unsigned int v;
+  asm volatile("mov.u32 %0, %smid;" : "=r"(v));
+  return v;
+}
 
 // Ticket order (topological; chosen so the next diagonal block is factored while the bulk of the
 // current block column is still being solved):
@@ -145,10 +174,10 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
   for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
 }
 
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(NTHREADS, CTAS_PER_SM)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
-             int static_sched, int solve_only) {
+             int static_sched, int solve_only, unsigned long long* __restrict__ trace) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -221,6 +250,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
     if (tid == 0) mbar_arrive(&sm.tq_empty[slot]);
     ++q;
     if (t < 0) break;
+    unsigned long long* tr = (trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
+    if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); tr[8] = smid(); }
     const TaskDesc d = decode_task(g, t, jcache);
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
@@ -246,6 +277,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
 #pragma unroll 1
     for (int it = 0; it < nstage; ++it) {
       if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+      if (tr && it == 0) tr[2] = clock64();
+      if (tr && it == nstage - (TILE / KC)) tr[9] = clock64();  // last chunk's data arrived
       const double* PA = &sm.stage[stage][0];
       const double* PB = &sm.stage[stage][KC * LDT];
 #pragma unroll
@@ -266,6 +299,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
 
+    if (tr) tr[3] = clock64();
     // acc -> Cs (column-major [c][r])
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt)
@@ -280,8 +314,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
     if (d.i == d.j) {
       // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------
       double* LTj = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
+      if (tr) tr[4] = clock64();
       if (solve_only) diag_inverse(sm, LTj, tid);
       else diag_factor(sm, Aij, LTj, g.ld, tid);
+      if (tr) tr[5] = clock64();
       __threadfence();
       fence_proxy_async();
       bar_named(1, NCONS);
@@ -293,10 +329,12 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
         }
         if (solve_only) atomicMax(done_b + d.j, d.j + 1);
         else st_release(done_b + d.j, d.j + 1);
+        if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
       }
     } else {
       // ---------- off-diagonal task: X = C * L_jj^-T ----------
       if (tid == 0) wait_counter(done_b + d.j, d.j + 1, &sched->error);
+      if (tr) tr[4] = clock64();
       bar_named(1, NCONS);
       const double* LT = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
 #pragma unroll 4
@@ -332,10 +370,12 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
           const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
           *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[mt][nt][0], x[mt][nt][1]);
         }
+      if (tr) tr[5] = clock64();
       __threadfence();
       fence_proxy_async();
       bar_named(1, NCONS);
       if (tid == 0) st_release(done_b + d.i, d.j + 1);
+      if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     }
   }
 }
@@ -364,7 +404,7 @@ static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
 }
 
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done, int* info,
-                SchedState* sched, int mode, int num_sms, int solve_only) {
+                SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace) {
   cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
   CUtensorMap tmap;
   if (!make_tmap(&tmap, g, mats)) return -1;
@@ -374,9 +414,10 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
   cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   int launches = 0;
   if (mode == 0) {
-    int grid = (int)(total < num_sms ? total : num_sms);
+    const long long slots = (long long)num_sms * CTAS_PER_SM;
+    int grid = (int)(total < slots ? total : slots);
     k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched, 0,
-                                                           (int)total, 0, solve_only);
+                                                           (int)total, 0, solve_only, trace);
     launches = 1;
   } else {
     // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
@@ -384,7 +425,7 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
       if (count <= 0) return;
       int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
       k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
-                                                             (int)begin, (int)(begin + count), 1, solve_only);
+                                                             (int)begin, (int)(begin + count), 1, solve_only, trace);
       ++launches;
     };
     run(0, g.batch);

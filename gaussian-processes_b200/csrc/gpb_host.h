@@ -28,6 +28,8 @@ struct gpb_ctx {
   gpb_ll* ll = nullptr;     size_t ll_n = 0;
   double* aux = nullptr;    size_t aux_doubles = 0;   // xstar / predictive outputs / MH state
   SchedState* sched = nullptr;
+  unsigned long long* trace = nullptr; size_t trace_n = 0;  // optional per-task schedule trace
+  int trace_on = 0; long long trace_tasks = 0;
   SchedState* h_sched = nullptr;  // pinned
   // pinned host staging
   Hyper* h_hyper = nullptr; size_t h_hyper_n = 0;

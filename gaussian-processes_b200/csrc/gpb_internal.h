@@ -21,7 +21,10 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 // mode 0: one persistent launch over all tasks; mode 1: two launches per block column.
 // Returns the number of kernel launches issued.
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done,
-                int* info, SchedState* sched, int mode, int num_sms, int solve_only = 0);
+                int* info, SchedState* sched, int mode, int num_sms, int solve_only = 0,
+                unsigned long long* trace = nullptr);
+constexpr int CHOL_TRACE_SLOTS = 10;
+long long chol_task_count(const Geom& g);
 // solve_only: the top square already holds a lower-triangular factor; only the appended rows are
 // solved (X = B L^-T) -- the matrix-level forward / backward substitutions.
 size_t chol_smem_bytes();

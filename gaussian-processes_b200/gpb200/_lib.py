@@ -19,7 +19,7 @@ EXPORTS = [
     "gpb_loglik", "gpb_loglik_batch", "gpb_ll_value", "gpb_predict", "gpb_distance_matrix",
     "gpb_build_cov", "gpb_potrf", "gpb_trsm_lower", "gpb_trsm_upper", "gpb_mh_run",
     "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
-    "gpb_last_timing", "gpb_set_sched", "gpb_version",
+    "gpb_last_timing", "gpb_set_sched", "gpb_set_trace", "gpb_get_trace", "gpb_version",
 ]
 
 
@@ -89,6 +89,9 @@ def load():
     L.gpb_philox_streams.argtypes = [C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
     L.gpb_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     L.gpb_set_sched.argtypes = [C.c_void_p, C.c_int]
+    L.gpb_set_trace.argtypes = [C.c_void_p, C.c_int]
+    L.gpb_get_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]
+    L.gpb_get_trace.restype = C.c_longlong
     _lib = L
     return L
 
@@ -155,6 +158,17 @@ class Context:
 
     def set_sched(self, mode):
         self._check(self.L.gpb_set_sched(self.h, int(mode)))
+
+    def set_trace(self, on):
+        self._check(self.L.gpb_set_trace(self.h, int(on)))
+
+    def get_trace(self):
+        """(tasks, 10) uint64 schedule trace of the last factorisation (see gpb200.h)."""
+        n = int(self.L.gpb_get_trace(self.h, None, 0))
+        out = np.zeros((n, 10), dtype=np.uint64)
+        if n:
+            self.L.gpb_get_trace(self.h, out.ctypes.data_as(C.c_void_p), n)
+        return out
 
     def launch_count(self):
         return int(self.L.gpb_launch_count(self.h))

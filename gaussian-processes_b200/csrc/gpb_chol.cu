@@ -28,13 +28,16 @@
 namespace gpb {
 
 #ifndef GPB_KC
-#define GPB_KC 16
+#define GPB_KC 8
 #endif
 #ifndef GPB_STAGES
-#define GPB_STAGES 2
+#define GPB_STAGES 4
 #endif
 #ifndef GPB_CTAS_PER_SM
 #define GPB_CTAS_PER_SM 2
+#endif
+#ifndef GPB_MINBLOCKS
+#define GPB_MINBLOCKS GPB_CTAS_PER_SM
 #endif
 constexpr int KC = GPB_KC;             // panel columns per pipeline stage
 constexpr int STAGES = GPB_STAGES;
@@ -174,7 +177,7 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
   for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
 }
 
-__global__ void __launch_bounds__(NTHREADS, CTAS_PER_SM)
+__global__ void __launch_bounds__(NTHREADS, GPB_MINBLOCKS)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
              int static_sched, int solve_only, unsigned long long* __restrict__ trace) {
@@ -274,6 +277,11 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       }
 
     const int nstage = (solve_only && d.i < g.nt) ? 0 : d.j * (TILE / KC);
+    // Stage release is DELAYED by one stage: ptxas schedules mbarrier.arrive right behind the last
+    // LDS of a stage without waiting for those loads to return, and with two CTAs per SM the
+    // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
+    // is being consumed guarantees every DMMA that read s has issued, i.e. its LDS completed.
+    int pend = -1;
 #pragma unroll 1
     for (int it = 0; it < nstage; ++it) {
       if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
@@ -295,7 +303,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
           for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.empty[stage]);
+      if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
+      pend = (int)stage;
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
 
@@ -310,6 +319,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       }
     if (tid == 0) sm.bad_col = -1;
     bar_named(1, NCONS);
+    if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);  // accumulators are stored: all reads done
 
     if (d.i == d.j) {
       // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------

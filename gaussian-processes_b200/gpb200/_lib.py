@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "libgpb200.so")
+# GPB200_LIB selects an alternative build of the SAME library (tuning variants); never a fallback
+LIB_PATH = os.environ.get("GPB200_LIB") or os.path.join(_PKG, "libgpb200.so")
 
 KIND_SE, KIND_WHITE, KIND_MATERN = 0, 1, 2
 FORMULA_AS_PARSED, FORMULA_GPML = 0, 1

@@ -222,8 +222,11 @@ def run_ours(args):
     achieved = args.steps * B * chol_flops(N_TRAIN) / (chol_ms * 1e-3) * 1e-12
 
     extra = {}
-    if rank == 0 and world == 1 and not args.no_extras:
-        extra = extras(ctx, ds, G, x, y)
+    if not args.no_extras:
+        if world == 1:
+            extra = extras_single_gpu(ctx, ds, G)
+        else:
+            extra = extras_multi_gpu(ctx, G, dist, local)   # collective: every rank takes part
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -260,36 +263,155 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def extras(ctx, ds, G, x, y):
-    """Secondary numbers named by BASELINE.json's metric string (not the headline line)."""
+def _mh_setup(n, lo, hi, seed, terms):
+    """Synthetic chain workload: shared dataset (as writeParallelChain shares it), SURVEY.md 8d."""
+    r = np.random.default_rng(seed)
+    x = r.uniform(lo, hi, size=(n, 2))
+    y = r.standard_normal(n) * 1.8  # timing only: parity of the chain itself is in tests/
+    return x, y, r
+
+
+def mh_bench(ctx, G, n, chains_total, iters, warm, terms, ig, seed, lo, hi, dist=None, local=0):
+    """MCMC iterations/s for `chains_total` chains sharded over the ranks (gpb_mh_run per rank,
+    then ONE NCCL all_gather of accepted states + ll + accept flags).  Timed end to end through
+    the ABI call with host buffers (streams H2D, chain outputs D2H), barrier on both sides, max
+    over ranks; the device time of the loop (CUDA events inside the library) is reported too."""
+    import torch
+    from gpb200 import chains as CH
+    world = dist.get_world_size() if dist is not None else 1
+    rank = dist.get_rank() if dist is not None else 0
+    x, y, r = _mh_setup(n, lo, hi, seed, terms)
+    ds = ctx.dataset(x, y)
+    first, count = CH.shard(chains_total, world, rank)
+    P = sum(2 if t[0] == "se" else 1 for t in terms)
+    rr = np.random.default_rng(seed + 17)
+    inits_all = []
+    for _ in range(chains_total):
+        z = rr.standard_normal(P) * 0.05
+        k, tl = 0, []
+        for t in terms:
+            if t[0] == "se":
+                tl.append((0, t[1] * math.exp(z[k]), t[2] * math.exp(z[k + 1]))); k += 2
+            else:
+                tl.append((1, t[1] * math.exp(z[k]), 0.0)); k += 1
+        inits_all.append(tl)
+    inits = inits_all[first:first + count]
+    dev = f"cuda:{local}"
+
+    def run(nit, seed2):
+        z, u = G.philox_streams(seed2, first, count, nit, P)
+        st, ll, acc, info = ds.mh_run(inits, ig, 0.05, z, u, on_notpd=1)
+        tdev = ctx.last_timing()[1]
+        if dist is not None and world > 1:
+            width = -(-chains_total // world)
+            block = np.zeros((nit, width, P + 2))
+            block[:, :count, :P] = st; block[:, :count, P] = ll; block[:, :count, P + 1] = acc
+            t = torch.from_numpy(block).to(dev)
+            out = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)
+            dist.all_gather_into_tensor(out, t)
+            out.cpu()
+        return acc, tdev
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None and world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run(warm, 100)
+    barrier()
+    t0 = time.perf_counter()
+    acc, tdev = run(iters, 101)
+    barrier()
+    wall = time.perf_counter() - t0
+    tt = torch.tensor([wall, tdev * 1e-3], dtype=torch.float64, device=dev)
+    if dist is not None and world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    wall, tdev = (float(v) for v in tt.cpu())
+    ds.close()
+    return {"iters_per_sec_e2e": iters / wall, "iters_per_sec_device": iters / tdev,
+            "chains_total": chains_total, "chains_per_gpu": count, "n": n, "iters": iters,
+            "accept_rate": float(np.mean(acc)), "factorisations_per_iter_per_chain": 1,
+            "gflop_per_iter": chains_total * chol_flops(n) * 1e-9}
+
+
+IG3 = [[3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]                       # SimulatedGp.scala:132-134
+IG5 = [[3.0, 4.0], [3.0, 6.0], [3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]
+C5_TERMS = [("se", 3.0, 5.5), ("se", 1.0, 0.8), ("white", 0.5)]
+
+
+def extras_single_gpu(ctx, ds, G):
+    """Secondary numbers named by BASELINE.json's metric string / configs (not the headline)."""
     out = {}
     rng = np.random.default_rng(5)
-    # latency mode: one proposal at a time (what a single MH chain sees)
-    for _ in range(3):
-        ds.loglik_batch([gterms(proposals(rng, 1)[0])])
-    t0 = time.perf_counter(); dev = 0.0
-    for _ in range(20):
-        ds.loglik_batch([gterms(proposals(rng, 1)[0])]); dev += sum(ctx.last_timing())
-    out["single_proposal_evals_per_sec_e2e"] = 20 / (time.perf_counter() - t0)
-    out["single_proposal_evals_per_sec_device"] = 20 / (dev * 1e-3)
-    # C3: 256 MH chains x n=1024 on this GPU
-    n, chains, iters = 1024, 256, 10
-    r2 = np.random.default_rng(3)
-    x3 = r2.uniform(-10, 10, size=(n, 2))
-    d2 = ((x3[:, None, :] - x3[None, :, :]) ** 2).sum(-1)
-    K = 3.0 * np.exp(-d2 / 30.25) + 0.501 * np.eye(n)
-    y3 = np.linalg.cholesky(K) @ r2.standard_normal(n)
-    ds3 = ctx.dataset(x3, y3)
-    ig = [[3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]
-    inits = [gterms(p) for p in proposals(r2, chains)]
-    z, u = G.philox_streams(9, 0, chains, iters, 3)
-    ds3.mh_run(inits, ig, 0.05, z[:2], u[:2], on_notpd=1)
-    t0 = time.perf_counter()
-    st, ll, acc, info = ds3.mh_run(inits, ig, 0.05, z, u, on_notpd=1)
-    dt = time.perf_counter() - t0
-    out["mcmc_iters_per_sec_256chains_n1024_1gpu"] = iters / dt
-    out["mcmc_accept_rate"] = float(acc.mean())
-    ds3.close()
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:  # never lose the headline line to a secondary measurement
+            out[name] = {"error": repr(e)[:200]}
+
+    def latency():
+        for _ in range(3):
+            ds.loglik_batch([gterms(proposals(rng, 1)[0])])
+        t0 = time.perf_counter(); dev = 0.0
+        for _ in range(20):
+            ds.loglik_batch([gterms(proposals(rng, 1)[0])]); dev += sum(ctx.last_timing())
+        return {"evals_per_sec_e2e": 20 / (time.perf_counter() - t0), "evals_per_sec_device": 20 / (dev * 1e-3)}
+
+    def c2_predict():
+        m = 4096
+        xs = rng.uniform(-10, 10, size=(m, 2))
+        ds.predict(gterms(TRUE_TERMS), xs, nugget=1e-6)
+        t0 = time.perf_counter()
+        ds.predict(gterms(TRUE_TERMS), xs, nugget=1e-6)
+        wall = time.perf_counter() - t0
+        t = ctx.last_timing()
+        fl = chol_flops(N_TRAIN) + float(N_TRAIN) ** 2 * m
+        return {"m": m, "points_per_sec_e2e": m / wall, "device_ms": sum(t), "factor_solve_tflops": fl / (t[1] * 1e-3) * 1e-12}
+
+    def c4():
+        import torch
+        n, m = 32768, 10000
+        r4 = np.random.default_rng(4)
+        x4 = r4.uniform(-30, 30, size=(n, 2)); y4 = r4.standard_normal(n) * 1.8
+        xs = r4.uniform(-30, 30, size=(m, 2))
+        ds4 = ctx.dataset(x4, y4)
+        res = {}
+        ds4.loglik_batch([gterms(TRUE_TERMS)])
+        t0 = time.perf_counter(); r = ds4.loglik_batch([gterms(TRUE_TERMS)])[0]; w = time.perf_counter() - t0
+        t = ctx.last_timing()
+        res["loglik_n32768"] = {"info": r.info, "wall_s": w, "build_ms": t[0], "factor_solve_ms": t[1],
+                                "factor_solve_tflops": chol_flops(n) / (t[1] * 1e-3) * 1e-12}
+        ds4.predict(gterms(TRUE_TERMS), xs, nugget=1e-6)
+        t0 = time.perf_counter(); mean, var, info = ds4.predict(gterms(TRUE_TERMS), xs, nugget=1e-6); w = time.perf_counter() - t0
+        t = ctx.last_timing()
+        fl = chol_flops(n) + float(n) ** 2 * m
+        res["predict_n32768_m10000"] = {"info": info, "wall_s": w, "points_per_sec_e2e": m / w, "build_ms": t[0],
+                                        "factor_solve_ms": t[1], "epilogue_ms": t[2],
+                                        "factor_solve_tflops": fl / (t[1] * 1e-3) * 1e-12}
+        ds4.close()
+        return res
+
+    guarded("c2_single_proposal_latency", latency)
+    guarded("c2_predict_m4096", c2_predict)
+    guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10))
+    guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64, 3, 1, C5_TERMS, IG5, 5, -15, 15))
+    guarded("c4", c4)
+    return out
+
+
+def extras_multi_gpu(ctx, G, dist, local):
+    """N > 1: the chain-parallel configs (C3 strong: 256 chains over N GPUs; C5 weak: 64 per GPU)."""
+    out = {}
+    world = dist.get_world_size()
+    for name, fn in (
+            ("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10, dist, local)),
+            ("c5_mcmc_64chains_per_gpu_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64 * world, 3, 1, C5_TERMS, IG5, 5, -15, 15, dist, local))):
+        try:
+            out[name] = fn()
+        except Exception as e:
+            out[name] = {"error": repr(e)[:200]}
     return out
 
 

@@ -24,6 +24,7 @@ Geom make_geom(int n, int dim, int m, bool with_rhs, int batch) {
   g.rt = g.ld / TILE;
   g.rhs_row = with_rhs ? g.npad + m : -1;
   g.batch = batch;
+  g.tgroup = batch;
   g.mat_stride = (size_t)g.ld * g.npad;
   return g;
 }
@@ -72,6 +73,15 @@ int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y
   return GPB_OK;
 }
 
+// Proposals per ticket group: enough tasks in flight to fill the machine, few enough that the
+// group's lower triangles (4 n^2 bytes each) stay L2-resident.  GPB_TICKET_GROUP overrides (tuning).
+static int ticket_group(const gpb_ctx* ctx, const Geom& g) {
+  static int env = -1;
+  if (env < 0) { const char* e = getenv("GPB_TICKET_GROUP"); env = e ? atoi(e) : 0; }
+  if (env > 0) return env < g.batch ? env : g.batch;
+  return g.batch;
+}
+
 int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
   unsigned long long* trace = nullptr;
   if (ctx->trace_on) {
@@ -81,7 +91,9 @@ int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
     cudaMemsetAsync(ctx->trace, 0, sizeof(unsigned long long) * ctx->trace_tasks * CHOL_TRACE_SLOTS, ctx->stream);
     trace = ctx->trace;
   }
-  const int nl = launch_chol(ctx->stream, g, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
+  Geom gg = g;
+  gg.tgroup = ticket_group(ctx, g);
+  const int nl = launch_chol(ctx->stream, gg, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
                              ctx->sched_mode, ctx->num_sms, solve_only, trace);
   if (nl < 0) {
     ctx->cuda_err = "cuTensorMapEncodeTiled failed (TMA descriptor of the workspace)";

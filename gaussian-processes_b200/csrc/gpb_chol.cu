@@ -89,23 +89,32 @@ __device__ __forceinline__ unsigned int smid() {
 //              B  diag(j+1,j+1)                                                  [if j+1 < nt]
 //              C  (i, j), i >= j+2
 // tickets before group j (j <= nt-1):  batch * (1 + j*rt - j(j+1)/2 + j)
-__device__ __host__ __forceinline__ long long group_start(const Geom& g, int j) {
-  return (long long)g.batch * (1 + (long long)j * g.rt - (long long)j * (j + 1) / 2 + j);
+__device__ __host__ __forceinline__ long long group_start(int batch, int rt, int j) {
+  return (long long)batch * (1 + (long long)j * rt - (long long)j * (j + 1) / 2 + j);
 }
+// Tickets are dealt out proposal-group by proposal-group (g.tgroup proposals per group, each group
+// in the column order above): the panels a group streams stay L2-resident, and the tail of one
+// group overlaps the head of the next.
 __device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcache) {
   TaskDesc d;
-  if (t < g.batch) { d.b = t; d.i = 0; d.j = 0; return d; }
-  while (jcache + 1 < g.nt && (long long)t >= group_start(g, jcache + 1)) ++jcache;
-  while (jcache > 0 && (long long)t < group_start(g, jcache)) --jcache;
+  const int per_mat = g.nt * g.rt - g.nt * (g.nt - 1) / 2;
+  const int per_group = g.tgroup * per_mat;
+  const int gi = t / per_group;
+  t -= gi * per_group;
+  const int b0 = gi * g.tgroup;
+  const int gb = min(g.tgroup, g.batch - b0);
+  if (t < gb) { d.b = b0 + t; d.i = 0; d.j = 0; return d; }
+  while (jcache + 1 < g.nt && (long long)t >= group_start(gb, g.rt, jcache + 1)) ++jcache;
+  while (jcache > 0 && (long long)t < group_start(gb, g.rt, jcache)) --jcache;
   const int j = jcache;
-  int local = t - (int)group_start(g, j);
-  const int nA = (j + 1 < g.rt) ? g.batch : 0, nB = (j + 1 < g.nt) ? g.batch : 0;
-  if (local < nA) { d.b = local; d.i = j + 1; d.j = j; return d; }
+  int local = t - (int)group_start(gb, g.rt, j);
+  const int nA = (j + 1 < g.rt) ? gb : 0, nB = (j + 1 < g.nt) ? gb : 0;
+  if (local < nA) { d.b = b0 + local; d.i = j + 1; d.j = j; return d; }
   local -= nA;
-  if (local < nB) { d.b = local; d.i = j + 1; d.j = j + 1; return d; }
+  if (local < nB) { d.b = b0 + local; d.i = j + 1; d.j = j + 1; return d; }
   local -= nB;
   const int per = g.rt - j - 2;
-  d.b = local / per; d.i = j + 2 + local % per; d.j = j;
+  d.b = b0 + local / per; d.i = j + 2 + local % per; d.j = j;
   return d;
 }
 
@@ -121,40 +130,102 @@ __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* erro
 }
 
 
-// Factor the stacked 128x64 [C; I] held in sm.Cs: each thread owns one row in registers, one
-// named barrier per column.  Top rows end as L_jj, bottom rows as L_jj^-T.  Right-looking with the
-// column left unscaled until the end of its step:  row[c2] -= (v_c(r)/a) * v_c(c2).
+// 1/a and 1/sqrt(a) from the hardware approximations (2^-23) plus two Newton steps each: the
+// reciprocal sits on the per-column dependency chain of the diagonal factorisation, where the
+// IEEE division / rsqrt subroutines would triple its length.
+__device__ __forceinline__ double fast_rcp(double a) {
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+  double e = fma(-a, x, 1.0);
+  x = fma(x, e, x);
+  e = fma(-a, x, 1.0);
+  return fma(x, e, x);
+}
+__device__ __forceinline__ double fast_rsqrt(double a) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double e = fma(-(a * y), y, 1.0);
+  y = fma(0.5 * y, e, y);
+  e = fma(-(a * y), y, 1.0);
+  return fma(0.5 * y, e, y);
+}
+
+// Factor the stacked 128x64 [C; I]: top rows (sm.Cs) end as L_jj, bottom rows (sm.Ls, starts as
+// the identity) as L_jj^-T -- the inverse costs no extra dependent step.  Blocked by 16 columns:
+//   panel   : one thread per stacked row keeps its 16 panel entries in registers; right-looking
+//             inside the panel with the column left unscaled until the end of its step
+//             (row[c2] -= (v_c(r)/a) v_c(c2)), ONE named barrier per column;
+//   trailing: rank-16 update of the remaining columns on the FP64 tensor cores, in place in
+//             shared memory.  Only 8 of the 16 row blocks are live at any step (top rows below
+//             the panel, bottom rows the panel has reached), two per warp.
+constexpr int PB = 16;
 __device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
                                          double* __restrict__ LT, int ld, int tid) {
-  double row[TILE];
-  const bool top = tid < TILE;
-#pragma unroll
-  for (int c = 0; c < TILE; ++c)
-    row[c] = top ? sm.Cs[c * LDT + tid] : ((tid - TILE) == c ? 1.0 : 0.0);
-#pragma unroll
-  for (int c = 0; c < TILE; ++c) {
-    double* cb = sm.colbuf[c & 1];
-    cb[tid] = row[c];
-    bar_named(1, NCONS);
-    const double a = cb[c];                     // pivot (Schur complement diagonal)
-    if (tid == c && !(a > 0.0) && sm.bad_col < 0) sm.bad_col = c;  // first bad column only
-    const double rs = rsqrt(a);
-    const double f = row[c] * (rs * rs);        // v_c(r) / a
-#pragma unroll
-    for (int c2 = c + 1; c2 < TILE; ++c2) row[c2] = fma(-f, cb[c2], row[c2]);
-    // scaled column entry; the pivot itself gets one Newton step so L_cc = sqrt(a) to ~0.5 ulp
-    double l = row[c] * rs;
-    if (tid == c) { const double s0 = a * rs; l = fma(0.5 * rs, fma(-s0, s0, a), s0); }
-    row[c] = l;
+  const int warp = tid >> 5, lane = tid & 31, gq = lane >> 2, tq = lane & 3;
+  for (int e = tid; e < TILE * TILE; e += NCONS) {
+    const int c = e >> 6, k = e & (TILE - 1);
+    sm.Ls[c * LDT + k] = (c == k) ? 1.0 : 0.0;
   }
-  if (top) {
+  double* Mrow = (tid < TILE) ? &sm.Cs[tid] : &sm.Ls[tid - TILE];  // entry (R, c) at Mrow[c * LDT]
+  bar_named(1, NCONS);
+#pragma unroll 1
+  for (int c0 = 0; c0 < TILE; c0 += PB) {
+    double p[PB];
 #pragma unroll
-    for (int c = 0; c < TILE; ++c)
-      if (c <= tid) Aij[(size_t)c * ld + tid] = row[c];
-  } else {
-    const int k = tid - TILE;
+    for (int q = 0; q < PB; ++q) p[q] = Mrow[(c0 + q) * LDT];
 #pragma unroll
-    for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
+    for (int q = 0; q < PB; ++q) {
+      double* cb = sm.colbuf[q & 1];
+      cb[tid] = p[q];
+      bar_named(1, NCONS);
+      const double a = cb[c0 + q];                 // pivot (Schur complement diagonal)
+      if (tid == c0 + q && !(a > 0.0) && sm.bad_col < 0) sm.bad_col = c0 + q;  // first bad column
+      const double f = p[q] * fast_rcp(a);         // v_c(r) / a
+#pragma unroll
+      for (int q2 = q + 1; q2 < PB; ++q2) p[q2] = fma(-f, cb[c0 + q2], p[q2]);
+      // off the chain: scaled column entry; the pivot gets one more Newton step (L_cc ~0.5 ulp)
+      const double rs = fast_rsqrt(a);
+      double l = p[q] * rs;
+      if (tid == c0 + q) { const double s0 = a * rs; l = fma(0.5 * rs, fma(-s0, s0, a), s0); }
+      p[q] = l;
+    }
+#pragma unroll
+    for (int q = 0; q < PB; ++q) Mrow[(c0 + q) * LDT] = p[q];
+    bar_named(1, NCONS);
+    const int cN = c0 + PB;                        // first trailing column
+    if (cN < TILE) {
+      // M(R, c2) -= sum_q P(R, q) P(c2, q)  for c2 >= cN;  D[m = c2][n = R], k = q
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int blk = 2 * warp + h;              // live row block 0..7
+        const int ntop = (TILE - cN) / 8;          // live top blocks: rows cN .. 63
+        double* base;                              // column-major [c][row], row offset folded in
+        if (blk < ntop) base = &sm.Cs[cN + 8 * blk];
+        else base = &sm.Ls[8 * (blk - ntop)];
+        double bf[PB / 4];
+#pragma unroll
+        for (int ks = 0; ks < PB / 4; ++ks) bf[ks] = base[(c0 + ks * 4 + tq) * LDT + gq];
+#pragma unroll 2
+        for (int c2 = cN; c2 < TILE; c2 += 8) {
+          double2* dp = reinterpret_cast<double2*>(&base[(c2 + gq) * LDT + 2 * tq]);
+          double2 dv = *dp;
+#pragma unroll
+          for (int ks = 0; ks < PB / 4; ++ks)
+            dmma884(dv.x, dv.y, -sm.Cs[(c0 + ks * 4 + tq) * LDT + c2 + gq], bf[ks]);
+          *dp = dv;
+        }
+      }
+      bar_named(1, NCONS);
+    }
+  }
+  // L_jj (lower triangle) and L_jj^-T out, coalesced along rows
+  {
+    const int r = tid & (TILE - 1), half = tid >> 6;
+#pragma unroll 4
+    for (int c = half; c < TILE; c += 2) {
+      if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
+      LT[c * TILE + r] = (c >= r) ? sm.Ls[c * LDT + r] : 0.0;
+    }
   }
 }
 
@@ -413,9 +484,11 @@ static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done, int* info,
+int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,
                 SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace) {
   cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+  Geom g = g_in;
+  if (mode != 0 || g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;  // debug mode: one group
   CUtensorMap tmap;
   if (!make_tmap(&tmap, g, mats)) return -1;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
@@ -440,7 +513,7 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
     };
     run(0, g.batch);
     for (int j = 0; j < g.nt; ++j) {
-      long long begin = group_start(g, j);
+      long long begin = group_start(g.batch, g.rt, j);
       const long long nA = (j + 1 < g.rt) ? g.batch : 0, nB = (j + 1 < g.nt) ? g.batch : 0;
       const long long nC = (long long)g.batch * (g.rt - j - 2 > 0 ? g.rt - j - 2 : 0);
       run(begin, nA); run(begin + nA, nB); run(begin + nA + nB, nC);

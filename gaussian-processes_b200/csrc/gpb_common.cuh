@@ -33,6 +33,7 @@ struct Geom {
   int nt, rt;           // tile columns (npad/TILE), tile rows (ld/TILE)
   int rhs_row;          // absolute row index of the rhs row (npad + m)
   int batch;
+  int tgroup;           // proposals per ticket group of the factorisation kernel (<= batch)
   size_t mat_stride;    // doubles between consecutive matrices
 };
 

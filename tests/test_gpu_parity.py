@@ -338,3 +338,56 @@ def test_full_size_c5_sum_of_kernels_n8192(ctx, oracle):
     S, C = np.log(np.diag(L)).sum(), n * 0.5 * math.log(2 * math.pi)
     assert r.info == 0 and rel(G.ll_value(r, 1), -0.5 * u @ u - S - C) < LL_RTOL
     ds.close()
+
+
+def test_full_size_c4_n32768_predictive_10k(ctx):
+    """configs[3]: single GP n=32768 (FP64 blocked Cholesky) + 10 000-point predictive mean/variance.
+    The CPU oracle would need hours at this size, so the twin is cuSOLVER/cuBLAS FP64 through torch
+    on the same device (an independent implementation of the same algebra), plus the
+    size-independent properties Q(2y) = 4 Q(y) and S(2y) = S(y)."""
+    import torch
+    from gpb200 import _lib as G
+    n, m = 32768, 10000
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator(device="cpu").manual_seed(4)
+    x = (torch.rand((n, 2), generator=gen, dtype=torch.float64) * 60.0 - 30.0)
+    xs = (torch.rand((m, 2), generator=gen, dtype=torch.float64) * 60.0 - 30.0)
+    z = torch.randn(n, generator=gen, dtype=torch.float64)
+    xd, xsd = x.to(dev), xs.to(dev)
+
+    def cov(a, b):
+        d = torch.cdist(a, b)
+        return 3.0 * torch.exp(-(d * d) / (5.5 * 5.5))
+
+    K = cov(xd, xd)
+    K.diagonal().add_(0.5 + 1e-3)            # white at d == 0 (no duplicates here) + nugget 1e-3
+    L = torch.linalg.cholesky(K)
+    y = (L @ z.to(dev))
+    u = torch.linalg.solve_triangular(L, y[:, None], upper=False)[:, 0]
+    Q_t, U1_t, S_t = float(u @ u), float(u.sum()), float(torch.log(L.diagonal()).sum())
+    ds = ctx.dataset(x.numpy(), y.cpu().numpy())
+    r = ds.loglik_batch([gterms(SE_W)], nugget=1e-3)[0]
+    assert r.info == 0 and r.n == n
+    C = n * 0.5 * math.log(2 * math.pi)
+    assert rel(G.ll_value(r, 1), -0.5 * Q_t - S_t - C) < LL_RTOL
+    assert rel(r.Q, Q_t) < LL_RTOL and rel(r.S, S_t) < LL_RTOL and abs(r.U1 - U1_t) < 1e-8
+    ds2 = ctx.dataset(x.numpy(), 2.0 * y.cpu().numpy())
+    r2 = ds2.loglik_batch([gterms(SE_W)], nugget=1e-3)[0]
+    assert rel(r2.Q, 4.0 * r.Q) < 1e-13 and r2.S == r.S
+    ds2.close()
+    # predictive (Predict.fit semantics: nugget 1e-6, raw y, var = k(0) - v.v)
+    K.diagonal().add_(1e-6 - 1e-3)
+    L = torch.linalg.cholesky(K)
+    del K
+    Ks = cov(xd, xsd)                         # n x m
+    V = torch.linalg.solve_triangular(L, Ks, upper=False)
+    u6 = torch.linalg.solve_triangular(L, y[:, None], upper=False)[:, 0]
+    mean_t = (V.T @ u6).cpu().numpy()
+    var_t = (3.5 - (V * V).sum(0)).cpu().numpy()
+    del V, Ks, L
+    torch.cuda.empty_cache()
+    mean, var, info = ds.predict(gterms(SE_W), xs.numpy(), nugget=1e-6)
+    assert info == 0
+    assert np.allclose(mean, mean_t, rtol=1e-7, atol=1e-8)
+    assert np.allclose(var, var_t, rtol=1e-7, atol=1e-8)
+    ds.close()

@@ -7,6 +7,15 @@ from gpb200 import _lib as G
 
 def gs(batch, rt, j): return batch * (1 + j * rt - j * (j + 1) // 2 + j)
 def decode(batch, nt, rt, t):
+    G = int(os.environ.get("GPB_TICKET_GROUP", "0")) or batch
+    G = min(G, batch)
+    per_group = G * (nt * rt - nt * (nt - 1) // 2)
+    gi, t = divmod(t, per_group)
+    gb = min(G, batch - gi * G)
+    b, i, j = decode1(gb, nt, rt, t)
+    return (b + gi * G, i, j)
+
+def decode1(batch, nt, rt, t):
     if t < batch: return (t, 0, 0)
     j = 0
     while j + 1 < nt and t >= gs(batch, rt, j + 1): j += 1

@@ -329,7 +329,9 @@ def mh_bench(ctx, G, n, chains_total, iters, warm, terms, ig, seed, lo, hi, dist
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     wall, tdev = (float(v) for v in tt.cpu())
     ds.close()
+    # the timed call also evaluates the initial state once (iters + 1 factorisations per chain)
     return {"iters_per_sec_e2e": iters / wall, "iters_per_sec_device": iters / tdev,
+            "evals_per_sec_device": (iters + 1) * chains_total / tdev,
             "chains_total": chains_total, "chains_per_gpu": count, "n": n, "iters": iters,
             "accept_rate": float(np.mean(acc)), "factorisations_per_iter_per_chain": 1,
             "gflop_per_iter": chains_total * chol_flops(n) * 1e-9}
@@ -396,7 +398,7 @@ def extras_single_gpu(ctx, ds, G):
     guarded("c2_single_proposal_latency", latency)
     guarded("c2_predict_m4096", c2_predict)
     guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10))
-    guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64, 3, 1, C5_TERMS, IG5, 5, -15, 15))
+    guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64, 8, 1, C5_TERMS, IG5, 5, -15, 15))
     guarded("c4", c4)
     return out
 
@@ -407,7 +409,7 @@ def extras_multi_gpu(ctx, G, dist, local):
     world = dist.get_world_size()
     for name, fn in (
             ("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10, dist, local)),
-            ("c5_mcmc_64chains_per_gpu_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64 * world, 3, 1, C5_TERMS, IG5, 5, -15, 15, dist, local))):
+            ("c5_mcmc_64chains_per_gpu_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64 * world, 8, 1, C5_TERMS, IG5, 5, -15, 15, dist, local))):
         try:
             out[name] = fn()
         except Exception as e:
@@ -430,7 +432,7 @@ def main():
         args.warmup = 1 if args.warmup is None else args.warmup
         run_reference(args)
     else:
-        args.steps = 20 if args.steps is None else args.steps
+        args.steps = 100 if args.steps is None else args.steps
         args.warmup = 3 if args.warmup is None else args.warmup
         run_ours(args)
 

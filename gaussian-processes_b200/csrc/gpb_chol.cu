@@ -56,6 +56,9 @@ struct __align__(128) CholSmem {
   double colbuf[2][2 * TILE];
   uint64_t full[STAGES], empty[STAGES];
   uint64_t tq_full[2], tq_empty[2];
+  uint64_t rel_full[2], rel_empty[2];   // consumer -> producer: "tile stored, publish it"
+  int* rel_ptr[2];
+  int rel_val[2];
   int taskq[2];
   int bad_col;
 };
@@ -248,6 +251,45 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
   for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
 }
 
+// Deferred publication.  A consumer group that has stored its tile does not wait for the stores
+// to become visible: it posts (counter, value) and moves on to the next task.  The producer lane,
+// which spends most of its time waiting anyway, drains the post: gpu-scope fence (cumulative over
+// the consumers' stores, ordered before it by the CTA barrier + mbarrier), proxy fence (the
+// readers are TMA loads), release store.  Every producer spin loop calls this, so a pending
+// publication can never be starved.
+struct RelState { int r; };
+__device__ __forceinline__ void service_release(CholSmem& sm, RelState& rs) {
+  for (;;) {
+    const int slot = rs.r & 1, par = (rs.r >> 1) & 1;
+    if (!mbar_test_wait(&sm.rel_full[slot], par)) return;
+    int* p = sm.rel_ptr[slot];
+    const int v = sm.rel_val[slot];
+    __threadfence();
+    fence_proxy_async();
+    st_release(p, v);
+    mbar_arrive(&sm.rel_empty[slot]);
+    ++rs.r;
+  }
+}
+__device__ __forceinline__ bool mbar_wait_serving(uint64_t* bar, uint32_t parity, CholSmem& sm, RelState& rs) {
+  for (uint32_t it = 0; it < (1u << 26); ++it) {
+    if (mbar_test_wait(bar, parity)) return true;
+    service_release(sm, rs);
+  }
+  return false;
+}
+__device__ __forceinline__ bool wait_counter_serving(const int* ctr, int need, int* error, CholSmem& sm, RelState& rs) {
+  if (ld_acquire(ctr) >= need) return true;
+  long long t0 = clock64();
+  for (;;) {
+    service_release(sm, rs);
+    if (ld_acquire(ctr) >= need) return true;
+    if (*(volatile int*)error) return false;
+    if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(error, 1); return false; }
+    __nanosleep(20);
+  }
+}
+
 __global__ void __launch_bounds__(NTHREADS, GPB_MINBLOCKS)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
@@ -260,6 +302,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
     tma_prefetch_desc(&tmap);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
     mbar_fence_init();
   }
   __syncthreads();
@@ -270,6 +313,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
   if (warp == NCONS / 32) {
     // =============================== producer warp ===============================
     int q = 0, static_next = task_begin + blockIdx.x;
+    RelState rs; rs.r = 0;
+    int posted = 0;   // tasks handed to the consumers that will post a publication
     for (;;) {
       int t;
       if (lane == 0) {
@@ -280,12 +325,13 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       t = __shfl_sync(0xffffffffu, t, 0);
       const int slot = q & 1, qpar = (q >> 1) & 1;
       if (lane == 0) {
-        if (!mbar_wait(&sm.tq_empty[slot], qpar ^ 1)) atomicExch(&sched->error, 2);
+        if (!mbar_wait_serving(&sm.tq_empty[slot], qpar ^ 1, sm, rs)) atomicExch(&sched->error, 2);
         sm.taskq[slot] = t;
         mbar_arrive(&sm.tq_full[slot]);
       }
       ++q;
       if (t < 0) break;
+      if (!solve_only) ++posted;
       const TaskDesc d = decode_task(g, t, jcache);
       if (solve_only && d.i < g.nt) continue;  // L is given: no accumulation for top-square tiles
       const int* done_b = done + (size_t)d.b * g.rt;
@@ -293,12 +339,12 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
         // one elected lane drives the ring: two TMA boxes per stage ({LDT rows x KC cols}: the
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
         for (int kc = 0; kc < d.j; ++kc) {
-          wait_counter(done_b + d.i, kc + 1, &sched->error);
-          wait_counter(done_b + d.j, kc + 1, &sched->error);
+          wait_counter_serving(done_b + d.i, kc + 1, &sched->error, sm, rs);
+          wait_counter_serving(done_b + d.j, kc + 1, &sched->error, sm, rs);
           fence_proxy_async();
 #pragma unroll 1
           for (int s = 0; s < TILE / KC; ++s) {
-            if (!mbar_wait(&sm.empty[stage], phase ^ 1)) atomicExch(&sched->error, 3);
+            if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
             mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
             const int col = kc * TILE + s * KC;
             tma_load_3d(&sm.stage[stage][0], &tmap, d.j * TILE, col, d.b, &sm.full[stage]);
@@ -309,13 +355,32 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       }
       __syncwarp();
     }
+    if (lane == 0) {
+      // drain: every task this CTA took must be published before the producer leaves
+      const long long t0 = clock64();
+      while (rs.r < posted) {
+        service_release(sm, rs);
+        if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(&sched->error, 6); break; }
+      }
+    }
     return;
   }
 
   // ================================= consumer warps =================================
   const int gq = lane >> 2, tq = lane & 3;          // DMMA fragment coordinates
   const int wc = warp >> 1, wr = warp & 1;          // warp's 32x32 sub-tile: c block, r block
-  int q = 0;
+  int q = 0, relc = 0;
+  // post (counter, value) for the producer lane to publish; all consumer stores are issued
+  auto post_release = [&](int* ptr, int val) {
+    const int rsl = relc & 1, rpar = (relc >> 1) & 1;
+    if (tid == 0) {
+      if (!mbar_wait(&sm.rel_empty[rsl], rpar ^ 1)) atomicExch(&sched->error, 7);
+      sm.rel_ptr[rsl] = ptr; sm.rel_val[rsl] = val;
+    }
+    bar_named(1, NCONS);               // every consumer's stores are ordered before the post
+    if (tid == 0) mbar_arrive(&sm.rel_full[rsl]);
+    ++relc;
+  };
   for (;;) {
     const int slot = q & 1, qpar = (q >> 1) & 1;
     if (!mbar_wait(&sm.tq_full[slot], qpar)) atomicExch(&sched->error, 4);
@@ -399,19 +464,17 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
       if (solve_only) diag_inverse(sm, LTj, tid);
       else diag_factor(sm, Aij, LTj, g.ld, tid);
       if (tr) tr[5] = clock64();
-      __threadfence();
-      fence_proxy_async();
-      bar_named(1, NCONS);
-      if (tid == 0) {
-        if (sm.bad_col >= 0) {
-          const int bad = d.j * TILE + sm.bad_col + 1;  // 1-based global pivot index
-          int old = atomicCAS(&info[d.b], 0, bad);
-          (void)old;
-        }
-        if (solve_only) atomicMax(done_b + d.j, d.j + 1);
-        else st_release(done_b + d.j, d.j + 1);
-        if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
+      if (solve_only) {
+        __threadfence();
+        fence_proxy_async();
+        bar_named(1, NCONS);
+        if (tid == 0) atomicMax(done_b + d.j, d.j + 1);
+      } else {
+        bar_named(1, NCONS);           // bad_col is final
+        if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, d.j * TILE + sm.bad_col + 1);  // 1-based pivot
+        post_release(done_b + d.j, d.j + 1);
       }
+      if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     } else {
       // ---------- off-diagonal task: X = C * L_jj^-T ----------
       if (tid == 0) wait_counter(done_b + d.j, d.j + 1, &sched->error);
@@ -452,10 +515,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
           *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[mt][nt][0], x[mt][nt][1]);
         }
       if (tr) tr[5] = clock64();
-      __threadfence();
-      fence_proxy_async();
-      bar_named(1, NCONS);
-      if (tid == 0) st_release(done_b + d.i, d.j + 1);
+      if (solve_only) {
+        __threadfence();
+        fence_proxy_async();
+        bar_named(1, NCONS);
+        if (tid == 0) st_release(done_b + d.i, d.j + 1);
+      } else {
+        post_release(done_b + d.i, d.j + 1);
+      }
       if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     }
   }

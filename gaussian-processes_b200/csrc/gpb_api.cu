@@ -32,7 +32,7 @@ Geom make_geom(int n, int dim, int m, bool with_rhs, int batch) {
 int ensure_workspace(gpb_ctx* ctx, const Geom& g) {
   int rc;
   if ((rc = grow(ctx, &ctx->mats, &ctx->mats_doubles, g.mat_stride * g.batch))) return rc;
-  if ((rc = grow(ctx, &ctx->linvt, &ctx->linvt_doubles, (size_t)g.batch * g.nt * TILE * TILE))) return rc;
+  if ((rc = grow(ctx, &ctx->linvt, &ctx->linvt_doubles, chol_linvt_doubles(g)))) return rc;
   if ((rc = grow(ctx, &ctx->done, &ctx->done_ints, (size_t)g.batch * g.rt))) return rc;
   if ((rc = grow(ctx, &ctx->info, &ctx->info_ints, (size_t)g.batch))) return rc;
   if ((rc = grow(ctx, &ctx->hyper, &ctx->hyper_n, (size_t)g.batch))) return rc;

@@ -31,7 +31,7 @@ namespace gpb {
 #define GPB_KC 8
 #endif
 #ifndef GPB_STAGES
-#define GPB_STAGES 4
+#define GPB_STAGES 8
 #endif
 #ifndef GPB_CTAS_PER_SM
 #define GPB_CTAS_PER_SM 2
@@ -45,6 +45,8 @@ constexpr int CTAS_PER_SM = GPB_CTAS_PER_SM;  // co-resident CTAs: one factors/s
 constexpr int NCONS = 128;             // consumer threads: 4 warps, 32x32 sub-tile each
 constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
 constexpr int STAGE_DOUBLES = 2 * KC * LDT;
+constexpr int SCOLS = 2 * KC;          // tile columns (of L_jj^-T, or of the diagonal scratch) one stage holds
+constexpr int LT_STAGES = TILE / SCOLS;  // stages that carry one 64 x 64 L_jj^-T tile
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
 constexpr int TRACE_SLOTS = 10;
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
@@ -52,7 +54,6 @@ constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 struct __align__(128) CholSmem {
   double stage[STAGES][STAGE_DOUBLES];  // [0..KC) panel j ("c" rows), [KC..2KC) panel i ("r" rows)
   double Cs[TILE * LDT];                // C tile, column-major [c][r]
-  double Ls[TILE * LDT];                // L_jj^-T tile, column-major [c][k]
   double colbuf[2][2 * TILE];
   uint64_t full[STAGES], empty[STAGES];
   uint64_t tq_full[2], tq_empty[2];
@@ -64,6 +65,7 @@ struct __align__(128) CholSmem {
 };
 
 size_t chol_smem_bytes() { return sizeof(CholSmem); }
+size_t chol_linvt_doubles(const Geom& g) { return (size_t)g.batch * g.nt * TILE * LDT; }
 long long chol_task_count(const Geom& g) {
   return (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
 }
@@ -153,8 +155,10 @@ __device__ __forceinline__ double fast_rsqrt(double a) {
   return fma(0.5 * y, e, y);
 }
 
-// Factor the stacked 128x64 [C; I]: top rows (sm.Cs) end as L_jj, bottom rows (sm.Ls, starts as
-// the identity) as L_jj^-T -- the inverse costs no extra dependent step.  Blocked by 16 columns:
+// Factor the stacked 128x64 [C; I]: top rows (sm.Cs) end as L_jj, bottom rows W (starts as the
+// identity) as L_jj^-T -- the inverse costs no extra dependent step.  W lives in LT_STAGES ring
+// stages the producer grants to the diagonal task (stage s0 + c / SCOLS holds columns c of W, pitch
+// LDT), so the kernel needs no second tile buffer.  Blocked by 16 columns:
 //   panel   : one thread per stacked row keeps its 16 panel entries in registers; right-looking
 //             inside the panel with the column left unscaled until the end of its step
 //             (row[c2] -= (v_c(r)/a) v_c(c2)), ONE named barrier per column;
@@ -162,20 +166,25 @@ __device__ __forceinline__ double fast_rsqrt(double a) {
 //             shared memory.  Only 8 of the 16 row blocks are live at any step (top rows below
 //             the panel, bottom rows the panel has reached), two per warp.
 constexpr int PB = 16;
-__device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
+static_assert(PB % SCOLS == 0 || SCOLS % PB == 0, "panel / stage column blocking");
+__device__ __forceinline__ double* wcol(CholSmem& sm, int s0, int c) {
+  return &sm.stage[(s0 + c / SCOLS) % STAGES][(c % SCOLS) * LDT];
+}
+__device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restrict__ Aij,
                                          double* __restrict__ LT, int ld, int tid) {
   const int warp = tid >> 5, lane = tid & 31, gq = lane >> 2, tq = lane & 3;
   for (int e = tid; e < TILE * TILE; e += NCONS) {
     const int c = e >> 6, k = e & (TILE - 1);
-    sm.Ls[c * LDT + k] = (c == k) ? 1.0 : 0.0;
+    wcol(sm, s0, c)[k] = (c == k) ? 1.0 : 0.0;
   }
-  double* Mrow = (tid < TILE) ? &sm.Cs[tid] : &sm.Ls[tid - TILE];  // entry (R, c) at Mrow[c * LDT]
+  const bool top = tid < TILE;
+  const int rr = top ? tid : tid - TILE;   // entry (R, c): top Cs[c * LDT + rr], bottom wcol(c)[rr]
   bar_named(1, NCONS);
 #pragma unroll 1
   for (int c0 = 0; c0 < TILE; c0 += PB) {
     double p[PB];
 #pragma unroll
-    for (int q = 0; q < PB; ++q) p[q] = Mrow[(c0 + q) * LDT];
+    for (int q = 0; q < PB; ++q) p[q] = top ? sm.Cs[(c0 + q) * LDT + rr] : wcol(sm, s0, c0 + q)[rr];
 #pragma unroll
     for (int q = 0; q < PB; ++q) {
       double* cb = sm.colbuf[q & 1];
@@ -189,11 +198,14 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
       // off the chain: scaled column entry; the pivot gets one more Newton step (L_cc ~0.5 ulp)
       const double rs = fast_rsqrt(a);
       double l = p[q] * rs;
-      if (tid == c0 + q) { const double s0 = a * rs; l = fma(0.5 * rs, fma(-s0, s0, a), s0); }
+      if (tid == c0 + q) { const double s0v = a * rs; l = fma(0.5 * rs, fma(-s0v, s0v, a), s0v); }
       p[q] = l;
     }
 #pragma unroll
-    for (int q = 0; q < PB; ++q) Mrow[(c0 + q) * LDT] = p[q];
+    for (int q = 0; q < PB; ++q) {
+      if (top) sm.Cs[(c0 + q) * LDT + rr] = p[q];
+      else wcol(sm, s0, c0 + q)[rr] = p[q];
+    }
     bar_named(1, NCONS);
     const int cN = c0 + PB;                        // first trailing column
     if (cN < TILE) {
@@ -202,15 +214,18 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
       for (int h = 0; h < 2; ++h) {
         const int blk = 2 * warp + h;              // live row block 0..7
         const int ntop = (TILE - cN) / 8;          // live top blocks: rows cN .. 63
-        double* base;                              // column-major [c][row], row offset folded in
-        if (blk < ntop) base = &sm.Cs[cN + 8 * blk];
-        else base = &sm.Ls[8 * (blk - ntop)];
+        const bool btop = blk < ntop;
+        const int r0 = btop ? cN + 8 * blk : 8 * (blk - ntop);
         double bf[PB / 4];
 #pragma unroll
-        for (int ks = 0; ks < PB / 4; ++ks) bf[ks] = base[(c0 + ks * 4 + tq) * LDT + gq];
+        for (int ks = 0; ks < PB / 4; ++ks) {
+          const int c = c0 + ks * 4 + tq;
+          bf[ks] = btop ? sm.Cs[c * LDT + r0 + gq] : wcol(sm, s0, c)[r0 + gq];
+        }
 #pragma unroll 2
         for (int c2 = cN; c2 < TILE; c2 += 8) {
-          double2* dp = reinterpret_cast<double2*>(&base[(c2 + gq) * LDT + 2 * tq]);
+          double* col = btop ? &sm.Cs[(c2 + gq) * LDT] : wcol(sm, s0, c2 + gq);
+          double2* dp = reinterpret_cast<double2*>(&col[r0 + 2 * tq]);
           double2 dv = *dp;
 #pragma unroll
           for (int ks = 0; ks < PB / 4; ++ks)
@@ -221,13 +236,13 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, double* __restrict__ Aij,
       bar_named(1, NCONS);
     }
   }
-  // L_jj (lower triangle) and L_jj^-T out, coalesced along rows
+  // L_jj (lower triangle) and L_jj^-T (pitch LDT, the layout the TMA boxes of the solves read) out
   {
     const int r = tid & (TILE - 1), half = tid >> 6;
 #pragma unroll 4
     for (int c = half; c < TILE; c += 2) {
       if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
-      LT[c * TILE + r] = (c >= r) ? sm.Ls[c * LDT + r] : 0.0;
+      LT[c * LDT + r] = (c >= r) ? wcol(sm, s0, c)[r] : 0.0;
     }
   }
 }
@@ -248,7 +263,7 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
     for (int c2 = c + 1; c2 < TILE; ++c2) row[c2] = fma(-xv, sm.Cs[c * LDT + c2], row[c2]);
   }
 #pragma unroll
-  for (int c = 0; c < TILE; ++c) LT[c * TILE + k] = (c >= k) ? row[c] : 0.0;
+  for (int c = 0; c < TILE; ++c) LT[c * LDT + k] = (c >= k) ? row[c] : 0.0;
 }
 
 // Deferred publication.  A consumer group that has stored its tile does not wait for the stores
@@ -291,7 +306,7 @@ __device__ __forceinline__ bool wait_counter_serving(const int* ctr, int need, i
 }
 
 __global__ void __launch_bounds__(NTHREADS, GPB_MINBLOCKS)
-k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
+k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapL, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
              int static_sched, int solve_only, unsigned long long* __restrict__ trace) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -300,6 +315,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
 
   if (tid == 0) {
     tma_prefetch_desc(&tmap);
+    tma_prefetch_desc(&tmapL);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
@@ -349,6 +365,29 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
             const int col = kc * TILE + s * KC;
             tma_load_3d(&sm.stage[stage][0], &tmap, d.j * TILE, col, d.b, &sm.full[stage]);
             tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col, d.b, &sm.full[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+        if (d.i != d.j) {
+          // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
+          // ring: LT_STAGES stages of SCOLS rows each, as soon as diag(j) is published
+          wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
+          fence_proxy_async();
+          const int row0 = (d.b * g.nt + d.j) * TILE;
+#pragma unroll 1
+          for (int s = 0; s < LT_STAGES; ++s) {
+            if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+            mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+            tma_load_2d(&sm.stage[stage][0], &tmapL, 0, row0 + s * SCOLS, &sm.full[stage]);
+            tma_load_2d(&sm.stage[stage][KC * LDT], &tmapL, 0, row0 + s * SCOLS + KC, &sm.full[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        } else if (!solve_only) {
+          // diagonal task: grant LT_STAGES empty stages as scratch for the stacked inverse rows
+#pragma unroll 1
+          for (int s = 0; s < LT_STAGES; ++s) {
+            if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+            mbar_arrive(&sm.full[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -459,61 +498,74 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
 
     if (d.i == d.j) {
       // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------
-      double* LTj = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
+      double* LTj = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * LDT);
       if (tr) tr[4] = clock64();
-      if (solve_only) diag_inverse(sm, LTj, tid);
-      else diag_factor(sm, Aij, LTj, g.ld, tid);
-      if (tr) tr[5] = clock64();
       if (solve_only) {
+        diag_inverse(sm, LTj, tid);
+        if (tr) tr[5] = clock64();
         __threadfence();
         fence_proxy_async();
         bar_named(1, NCONS);
         if (tid == 0) atomicMax(done_b + d.j, d.j + 1);
       } else {
-        bar_named(1, NCONS);           // bad_col is final
+        const int s0 = (int)stage;     // first of the LT_STAGES scratch stages the producer grants
+#pragma unroll 1
+        for (int s = 0; s < LT_STAGES; ++s) {
+          if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        diag_factor(sm, s0, Aij, LTj, g.ld, tid);
+        if (tr) tr[5] = clock64();
+        bar_named(1, NCONS);           // bad_col is final; every read of the scratch stages is done
         if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, d.j * TILE + sm.bad_col + 1);  // 1-based pivot
         post_release(done_b + d.j, d.j + 1);
+        fence_proxy_async();           // generic writes to the scratch stages before TMA refills them
+        __syncwarp();
+        if (lane == 0)
+          for (int s = 0; s < LT_STAGES; ++s) mbar_arrive(&sm.empty[(s0 + s) % STAGES]);
       }
       if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     } else {
-      // ---------- off-diagonal task: X = C * L_jj^-T ----------
-      if (tid == 0) wait_counter(done_b + d.j, d.j + 1, &sched->error);
-      if (tr) tr[4] = clock64();
-      bar_named(1, NCONS);
-      const double* LT = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * TILE);
-#pragma unroll 4
-      for (int e = tid; e < TILE * TILE / 2; e += NCONS) {
-        const int c = e / (TILE / 2), k2 = (e % (TILE / 2)) * 2;
-        double2 v = ld_cg2(LT + c * TILE + k2);
-        *reinterpret_cast<double2*>(&sm.Ls[c * LDT + k2]) = v;
-      }
-      bar_named(1, NCONS);
-      double x[4][4][2];
+      // ---------- off-diagonal task: X = C * L_jj^-T, L_jj^-T streamed through the ring ----------
+      // stage s carries rows c = s*SCOLS .. of L_jj^-T; each warp solves those columns of X for its
+      // 16 rows r and stores them straight to global memory
+      constexpr int CT = SCOLS / 8;
+#pragma unroll 1
+      for (int s = 0; s < LT_STAGES; ++s) {
+        if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+        if (tr && s == 0) tr[4] = clock64();
+        const double* LTs = &sm.stage[stage][0];
+        double x[CT][2][2];
 #pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
+        for (int ct = 0; ct < CT; ++ct)
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) x[mt][nt][0] = x[mt][nt][1] = 0.0;
-      const int kend = wc * 32 + 32;   // L^-T(k, c) == 0 for k > c
-#pragma unroll 4
-      for (int k0 = 0; k0 < kend; k0 += 4) {
-        const int k = k0 + tq;
-        double a[4], bb[4];
+          for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
+        const int kend = (s + 1) * SCOLS;   // L^-T(k, c) == 0 for k > c
+#pragma unroll 2
+        for (int k0 = 0; k0 < kend; k0 += 4) {
+          const int k = k0 + tq;
+          double a[CT], bb[2];
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) a[mt] = sm.Ls[(wc * 32 + mt * 8 + gq) * LDT + k];
+          for (int ct = 0; ct < CT; ++ct) a[ct] = LTs[(ct * 8 + gq) * LDT + k];
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) bb[nt] = sm.Cs[k * LDT + wr * 32 + nt * 8 + gq];
+          for (int nt = 0; nt < 2; ++nt) bb[nt] = sm.Cs[k * LDT + warp * 16 + nt * 8 + gq];
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
+          for (int ct = 0; ct < CT; ++ct)
 #pragma unroll
-          for (int nt = 0; nt < 4; ++nt) dmma884(x[mt][nt][0], x[mt][nt][1], a[mt], bb[nt]);
-      }
-#pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
-          const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
-          *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[mt][nt][0], x[mt][nt][1]);
+            for (int nt = 0; nt < 2; ++nt) dmma884(x[ct][nt][0], x[ct][nt][1], a[ct], bb[nt]);
         }
+#pragma unroll
+        for (int ct = 0; ct < CT; ++ct)
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            const int c = s * SCOLS + ct * 8 + gq, r = warp * 16 + nt * 8 + 2 * tq;
+            *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[ct][nt][0], x[ct][nt][1]);
+          }
+        // the stores above consumed every DMMA of this stage, so its LDS have completed
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
       if (tr) tr[5] = clock64();
       if (solve_only) {
         __threadfence();
@@ -528,20 +580,39 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, Geom g, double* __restric
   }
 }
 
-static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
-  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                               const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                               CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                               CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                             const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                             CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                             CUtensorMapFloatOOBfill);
+static EncodeFn tmap_encoder() {
   static EncodeFn encode = nullptr;
   if (!encode) {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
         qres != cudaDriverEntryPointSuccess || !fn)
-      return false;
+      return nullptr;
     encode = reinterpret_cast<EncodeFn>(fn);
   }
+  return encode;
+}
+
+// L_jj^-T tiles: [batch * nt * TILE rows][LDT] doubles (rows c, pitch LDT), box {LDT, KC}.
+static bool make_tmap_linvt(CUtensorMap* tm, const Geom& g, double* linvt) {
+  EncodeFn encode = tmap_encoder();
+  if (!encode) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)LDT, (cuuint64_t)g.batch * g.nt * TILE};
+  const cuuint64_t strides[1] = {(cuuint64_t)LDT * sizeof(double)};
+  const cuuint32_t box[2] = {(cuuint32_t)LDT, (cuuint32_t)KC};
+  const cuuint32_t estr[2] = {1u, 1u};
+  return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, linvt, dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
+  EncodeFn encode = tmap_encoder();
+  if (!encode) return false;
   const cuuint64_t dims[3] = {(cuuint64_t)g.ld, (cuuint64_t)g.npad, (cuuint64_t)g.batch};
   const cuuint64_t strides[2] = {(cuuint64_t)g.ld * sizeof(double), (cuuint64_t)g.mat_stride * sizeof(double)};
   const cuuint32_t box[3] = {(cuuint32_t)LDT, (cuuint32_t)KC, 1u};
@@ -558,6 +629,8 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   if (mode != 0 || g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;  // debug mode: one group
   CUtensorMap tmap;
   if (!make_tmap(&tmap, g, mats)) return -1;
+  CUtensorMap tmapL;
+  if (!make_tmap_linvt(&tmapL, g, linvt)) return -1;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
   cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
   cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
@@ -566,7 +639,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   if (mode == 0) {
     const long long slots = (long long)num_sms * CTAS_PER_SM;
     int grid = (int)(total < slots ? total : slots);
-    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched, 0,
+    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
                                                            (int)total, 0, solve_only, trace);
     launches = 1;
   } else {
@@ -574,7 +647,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     auto run = [&](long long begin, long long count) {
       if (count <= 0) return;
       int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
-      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, g, mats, linvt, done, info, sched,
+      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
                                                              (int)begin, (int)(begin + count), 1, solve_only, trace);
       ++launches;
     };

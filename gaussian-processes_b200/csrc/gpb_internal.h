@@ -16,7 +16,7 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 
 // Tile Cholesky + panel solves of the tall system (gpb_chol.cu).
 //   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final)
-//   linvt  [batch][nt][TILE*TILE]  inverse-transposes of the diagonal blocks (side output)
+//   linvt  [batch][nt][TILE][LDT]  inverse-transposes of the diagonal blocks (side output, pitch LDT)
 //   info   [batch]      first non-positive pivot (1-based, LAPACK) or 0
 // mode 0: one persistent launch over all tasks; mode 1: two launches per block column.
 // Returns the number of kernel launches issued.
@@ -28,6 +28,8 @@ long long chol_task_count(const Geom& g);
 // solve_only: the top square already holds a lower-triangular factor; only the appended rows are
 // solved (X = B L^-T) -- the matrix-level forward / backward substitutions.
 size_t chol_smem_bytes();
+// doubles of the L_jj^-T side buffer (tiles of TILE rows x LDT pitch)
+size_t chol_linvt_doubles(const Geom& g);
 
 // Likelihood reductions Q, U1, S per proposal (gpb_epilogue.cu).
 void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, const int* info,

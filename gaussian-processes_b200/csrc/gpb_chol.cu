@@ -28,10 +28,10 @@
 namespace gpb {
 
 #ifndef GPB_KC
-#define GPB_KC 8
+#define GPB_KC 16
 #endif
 #ifndef GPB_STAGES
-#define GPB_STAGES 8
+#define GPB_STAGES 4
 #endif
 #ifndef GPB_CTAS_PER_SM
 #define GPB_CTAS_PER_SM 2
@@ -75,7 +75,7 @@ struct TaskDesc { int b, i, j; };
 // Optional per-task trace (debug builds of the schedule analysis; trace == nullptr in production):
 // [0] globaltimer at receipt, [1] clock at receipt, [2] first stage landed, [3] contraction done,
 // [4] dependency on the diagonal block satisfied, [5] factor / solve done, [6] clock at release,
-// [7] globaltimer at release, [8] SM id, [9] last chunk's first stage landed.
+// [7] globaltimer at release, [8] main-loop stages that were not ready at first probe, [9] cycles the main loop spent blocked on stage data.
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long v;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
@@ -166,9 +166,10 @@ __device__ __forceinline__ double fast_rsqrt(double a) {
 //             shared memory.  Only 8 of the 16 row blocks are live at any step (top rows below
 //             the panel, bottom rows the panel has reached), two per warp.
 constexpr int PB = 16;
-static_assert(PB % SCOLS == 0 || SCOLS % PB == 0, "panel / stage column blocking");
+static_assert(SCOLS % 8 == 0, "a stage holds whole 8-column blocks of the scratch tile");
 __device__ __forceinline__ double* wcol(CholSmem& sm, int s0, int c) {
-  return &sm.stage[(s0 + c / SCOLS) % STAGES][(c % SCOLS) * LDT];
+  const unsigned uc = (unsigned)c;
+  return &sm.stage[((unsigned)s0 + uc / SCOLS) % STAGES][(uc % SCOLS) * LDT];
 }
 __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restrict__ Aij,
                                          double* __restrict__ LT, int ld, int tid) {
@@ -183,8 +184,13 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
 #pragma unroll 1
   for (int c0 = 0; c0 < TILE; c0 += PB) {
     double p[PB];
+    if (top) {
 #pragma unroll
-    for (int q = 0; q < PB; ++q) p[q] = top ? sm.Cs[(c0 + q) * LDT + rr] : wcol(sm, s0, c0 + q)[rr];
+      for (int q = 0; q < PB; ++q) p[q] = sm.Cs[(c0 + q) * LDT + rr];
+    } else {
+#pragma unroll
+      for (int q = 0; q < PB; ++q) p[q] = wcol(sm, s0, c0 + q)[rr];
+    }
 #pragma unroll
     for (int q = 0; q < PB; ++q) {
       double* cb = sm.colbuf[q & 1];
@@ -201,10 +207,12 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       if (tid == c0 + q) { const double s0v = a * rs; l = fma(0.5 * rs, fma(-s0v, s0v, a), s0v); }
       p[q] = l;
     }
+    if (top) {
 #pragma unroll
-    for (int q = 0; q < PB; ++q) {
-      if (top) sm.Cs[(c0 + q) * LDT + rr] = p[q];
-      else wcol(sm, s0, c0 + q)[rr] = p[q];
+      for (int q = 0; q < PB; ++q) sm.Cs[(c0 + q) * LDT + rr] = p[q];
+    } else {
+#pragma unroll
+      for (int q = 0; q < PB; ++q) wcol(sm, s0, c0 + q)[rr] = p[q];
     }
     bar_named(1, NCONS);
     const int cN = c0 + PB;                        // first trailing column
@@ -224,7 +232,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
         }
 #pragma unroll 2
         for (int c2 = cN; c2 < TILE; c2 += 8) {
-          double* col = btop ? &sm.Cs[(c2 + gq) * LDT] : wcol(sm, s0, c2 + gq);
+          double* col = btop ? &sm.Cs[(c2 + gq) * LDT] : wcol(sm, s0, c2) + gq * LDT;
           double2* dp = reinterpret_cast<double2*>(&col[r0 + 2 * tq]);
           double2 dv = *dp;
 #pragma unroll
@@ -287,20 +295,25 @@ __device__ __forceinline__ void service_release(CholSmem& sm, RelState& rs) {
   }
 }
 __device__ __forceinline__ bool mbar_wait_serving(uint64_t* bar, uint32_t parity, CholSmem& sm, RelState& rs) {
-  for (uint32_t it = 0; it < (1u << 26); ++it) {
-    if (mbar_test_wait(bar, parity)) return true;
+  // sleep in hardware (<= ~0.3 us per try) instead of spinning: a busy producer lane steals issue
+  // slots and SYNCS bandwidth from the consumer warp that shares its scheduler
+  for (uint32_t it = 0; it < (1u << 23); ++it) {
+    if (mbar_try_wait_ns(bar, parity, 300)) return true;
     service_release(sm, rs);
   }
   return false;
 }
-__device__ __forceinline__ bool wait_counter_serving(const int* ctr, int need, int* error, CholSmem& sm, RelState& rs) {
-  if (ld_acquire(ctr) >= need) return true;
+// Returns the observed counter value (>= need), or -1 on error / watchdog.
+__device__ __forceinline__ int wait_counter_serving(const int* ctr, int need, int* error, CholSmem& sm, RelState& rs) {
+  int v = ld_acquire(ctr);
+  if (v >= need) return v;
   long long t0 = clock64();
   for (;;) {
     service_release(sm, rs);
-    if (ld_acquire(ctr) >= need) return true;
-    if (*(volatile int*)error) return false;
-    if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(error, 1); return false; }
+    v = ld_acquire(ctr);
+    if (v >= need) return v;
+    if (*(volatile int*)error) return -1;
+    if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(error, 1); return -1; }
     __nanosleep(20);
   }
 }
@@ -354,10 +367,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       if (lane == 0) {
         // one elected lane drives the ring: two TMA boxes per stage ({LDT rows x KC cols}: the
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
+        // progress counters only grow: poll again only when the last value seen is not enough
+        int seen_i = 0, seen_j = 0;
         for (int kc = 0; kc < d.j; ++kc) {
-          wait_counter_serving(done_b + d.i, kc + 1, &sched->error, sm, rs);
-          wait_counter_serving(done_b + d.j, kc + 1, &sched->error, sm, rs);
-          fence_proxy_async();
+          bool polled = false;
+          if (seen_i < kc + 1) { seen_i = wait_counter_serving(done_b + d.i, kc + 1, &sched->error, sm, rs); polled = true; }
+          if (seen_j < kc + 1) { seen_j = wait_counter_serving(done_b + d.j, kc + 1, &sched->error, sm, rs); polled = true; }
+          if (seen_i < 0 || seen_j < 0) { seen_i = seen_j = 1 << 30; }   // error: drain without waiting
+          if (polled) fence_proxy_async();
 #pragma unroll 1
           for (int s = 0; s < TILE / KC; ++s) {
             if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
@@ -371,7 +388,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         if (d.i != d.j) {
           // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
           // ring: LT_STAGES stages of SCOLS rows each, as soon as diag(j) is published
-          wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
+          if (seen_j < d.j + 1) wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
           fence_proxy_async();
           const int row0 = (d.b * g.nt + d.j) * TILE;
 #pragma unroll 1
@@ -429,7 +446,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     ++q;
     if (t < 0) break;
     unsigned long long* tr = (trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
-    if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); tr[8] = smid(); }
+    if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); }
     const TaskDesc d = decode_task(g, t, jcache);
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
@@ -457,33 +474,60 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
     // is being consumed guarantees every DMMA that read s has issued, i.e. its LDS completed.
     int pend = -1;
+    int not_ready = 0;
+    // fast path: the stage is almost always there already (test_wait is a plain probe; try_wait
+    // costs ~100 cycles even on a completed phase)
+    auto wait_full = [&](uint32_t st, uint32_t ph) {
+      if (mbar_test_wait(&sm.full[st], ph)) return;
+      ++not_ready;
+      if (!mbar_wait(&sm.full[st], ph)) atomicExch(&sched->error, 5);
+    };
+    auto load_frag = [&](const double* P, int ks, double (&a)[4], double (&bb)[4]) {
+      const int k = ks * 4 + tq;
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) a[mt] = -P[k * LDT + wc * 32 + mt * 8 + gq];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) bb[nt] = P[(KC + k) * LDT + wr * 32 + nt * 8 + gq];
+    };
+    if (nstage > 0) {
+      wait_full(stage, phase);
+      if (tr) tr[2] = clock64();
+      double a[4], bb[4];
+      load_frag(&sm.stage[stage][0], 0, a, bb);
 #pragma unroll 1
-    for (int it = 0; it < nstage; ++it) {
-      if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
-      if (tr && it == 0) tr[2] = clock64();
-      if (tr && it == nstage - (TILE / KC)) tr[9] = clock64();  // last chunk's data arrived
-      const double* PA = &sm.stage[stage][0];
-      const double* PB = &sm.stage[stage][KC * LDT];
+      for (int it = 0; it < nstage; ++it) {
+        const double* P = &sm.stage[stage][0];
+        uint32_t nst = stage + 1, nph = phase;
+        if (nst == STAGES) { nst = 0; nph ^= 1; }
 #pragma unroll
-      for (int ks = 0; ks < KC / 4; ++ks) {
-        const int k = ks * 4 + tq;
-        double a[4], bb[4];
+        for (int ks = 0; ks < KC / 4; ++ks) {
+          // fragments of the next k-step (or of the next stage's first k-step) are fetched before
+          // this step's 16 DMMAs issue, so neither the LDS latency nor the barrier probe is exposed
+          double an[4], bn[4];
+          if (ks + 1 < KC / 4) {
+            load_frag(P, ks + 1, an, bn);
+          } else if (it + 1 < nstage) {
+            wait_full(nst, nph);
+            load_frag(&sm.stage[nst][0], 0, an, bn);
+          } else {
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) a[mt] = -PA[k * LDT + wc * 32 + mt * 8 + gq];
+            for (int i = 0; i < 4; ++i) { an[i] = 0.0; bn[i] = 0.0; }
+          }
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) bb[nt] = PB[k * LDT + wr * 32 + nt * 8 + gq];
+          for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
+            for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
 #pragma unroll
-          for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+          for (int i = 0; i < 4; ++i) { a[i] = an[i]; bb[i] = bn[i]; }
+        }
+        __syncwarp();
+        if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
+        pend = (int)stage;
+        stage = nst; phase = nph;
       }
-      __syncwarp();
-      if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
-      pend = (int)stage;
-      if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
 
-    if (tr) tr[3] = clock64();
+    if (tr) { tr[3] = clock64(); tr[8] = (unsigned long long)not_ready; tr[9] = 0; }
     // acc -> Cs (column-major [c][r])
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt)
@@ -511,7 +555,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         const int s0 = (int)stage;     // first of the LT_STAGES scratch stages the producer grants
 #pragma unroll 1
         for (int s = 0; s < LT_STAGES; ++s) {
-          if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+          wait_full(stage, phase);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         diag_factor(sm, s0, Aij, LTj, g.ld, tid);
@@ -532,7 +576,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       constexpr int CT = SCOLS / 8;
 #pragma unroll 1
       for (int s = 0; s < LT_STAGES; ++s) {
-        if (!mbar_wait(&sm.full[stage], phase)) atomicExch(&sched->error, 5);
+        wait_full(stage, phase);
         if (tr && s == 0) tr[4] = clock64();
         const double* LTs = &sm.stage[stage][0];
         double x[CT][2][2];

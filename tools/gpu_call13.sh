@@ -1,0 +1,7 @@
+#!/bin/bash
+rm -f gpurun_out/c13.log
+timeout 300 python tools/stress_small.py >> gpurun_out/c13.log 2>&1
+timeout 300 python tools/c3_breakdown.py >> gpurun_out/c13.log 2>&1
+timeout 300 python tools/trace_analyze.py 1024 256 >> gpurun_out/c13.log 2>&1
+timeout 300 python tools/trace_analyze.py 4096 8 >> gpurun_out/c13.log 2>&1
+timeout 300 python tools/trace_analyze.py 4096 1 >> gpurun_out/c13.log 2>&1

@@ -55,7 +55,8 @@ def main():
         print("   recv->first data   us: mean %.2f  p50 %.2f  p90 %.2f" % tuple(np.percentile(us(t[has, 2] - t[has, 1]), [50, 50, 90]) if has.any() else (0, 0, 0)))
         ml = us(t[has, 3] - t[has, 2]); ch = j[has]
         print("   mainloop us per chunk: mean %.2f  p50 %.2f p90 %.2f (ideal 2.08)" % (np.mean(ml / ch), np.median(ml / ch), np.percentile(ml / ch, 90)))
-        print("   last chunk data->mainloop end us: p50 %.2f p90 %.2f" % tuple(np.percentile(us(t[has, 3] - t[has, 9]), [50, 90])))
+        nst = (j[has] * 4).sum()
+        print("   mainloop blocked on data: %.1f%% of mainloop time; %.1f%% of stages not ready at first probe, mean wait %.2f us when not ready" % (100.0 * t[has, 9].sum() / max(1, (t[has, 3] - t[has, 2]).sum()), 100.0 * t[has, 8].sum() / max(1, nst), us(t[has, 9].sum() / max(1, t[has, 8].sum()))))
         print("   mainloop end->dep ok  us: p50 %.2f  p90 %.2f  mean %.2f" % (*np.percentile(us(t[:, 4] - t[:, 3]), [50, 90]), us(t[:, 4] - t[:, 3]).mean()))
         print("   dep ok->compute done  us: p50 %.2f  p90 %.2f" % tuple(np.percentile(us(t[:, 5] - t[:, 4]), [50, 90])))
         print("   compute done->release us: p50 %.2f  p90 %.2f" % tuple(np.percentile(us(t[:, 6] - t[:, 5]), [50, 90])))
@@ -63,7 +64,7 @@ def main():
     # busy fraction per SM
     span = (tr[:, 7].max() - g0) / 1e3
     busy = us(tr[:, 6] - tr[:, 1]).sum()
-    print(f"kernel span {span:.1f} us; sum task time {busy:.1f} us over {len(np.unique(tr[:,8]))} SMs -> avg CTA busy {busy/span:.1f}")
+    print(f"kernel span {span:.1f} us; sum task time {busy:.1f} us -> avg CTA busy {busy/span:.1f}")
     if B == 1:
         # critical chain: release time of diag(j) relative to start
         d = {(dec[t, 1], dec[t, 2]): t for t in range(T)}
@@ -72,5 +73,5 @@ def main():
         for j in (8, 32, 56):
             if j + 1 >= nt: continue
             a = tr[d[(j + 1, j)]]; b = tr[d[(j + 1, j + 1)]]; dj = tr[d[(j, j)]]
-            print(f"  col {j}: diag({j}) rel {(dj[7]-g0)/1e3:.1f} | A recv {(a[0]-g0)/1e3:.1f} rel {(a[7]-g0)/1e3:.1f} (dep->done {us(a[5]-a[4]):.1f}, done->rel {us(a[6]-a[5]):.1f}) | diag({j+1}) recv {(b[0]-g0)/1e3:.1f} lastchunk-data->mlend {us(b[3]-b[9]):.1f} factor {us(b[5]-b[4]):.1f} rel {(b[7]-g0)/1e3:.1f}")
+            print(f"  col {j}: diag({j}) rel {(dj[7]-g0)/1e3:.1f} | A recv {(a[0]-g0)/1e3:.1f} rel {(a[7]-g0)/1e3:.1f} (dep->done {us(a[5]-a[4]):.1f}, done->rel {us(a[6]-a[5]):.1f}) | diag({j+1}) recv {(b[0]-g0)/1e3:.1f} factor {us(b[5]-b[4]):.1f} rel {(b[7]-g0)/1e3:.1f}")
 main()

@@ -39,7 +39,7 @@ __device__ __forceinline__ double cov_of_dist(const Hyper& h, double d) {
 __global__ void __launch_bounds__(256)
 k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         const double* __restrict__ xstar, const Hyper* __restrict__ hyper, double nugget,
-        double* __restrict__ mats, int mode, int full) {
+        double* __restrict__ mats, int mode, int full, const double* __restrict__ rows) {
   const int ti = blockIdx.x / g.nt, tj = blockIdx.x % g.nt;
   if (!full && ti < g.nt && tj > ti) return;  // strictly-upper tiles are never read
   const int b = blockIdx.y;
@@ -81,11 +81,12 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
   const int rl = tid & (TILE - 1);
   const int R = ti * TILE + rl;
   const double r0 = rx[0][rl], r1 = rx[1][rl];
-  // row class: 0 training, 1 padding (identity), 2 test point, 3 rhs row, 4 zero
+  // row class: 0 training, 1 padding (identity), 2 test point, 3 rhs row, 4 zero, 5 explicit row
   int rclass;
   if (R < g.n) rclass = 0;
   else if (R < g.npad) rclass = 1;
   else if (R - g.npad < g.m) rclass = 2;
+  else if (R - g.npad - g.m < g.design) rclass = 5;
   else if (R == g.rhs_row) rclass = 3;
   else rclass = 4;
 
@@ -110,6 +111,8 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         v = cov_of_dist(h, d);
         if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);  // GaussianProcess.scala:117-118
       }
+    } else if (rclass == 5) {
+      v = rows[(size_t)(R - g.npad - g.m) * g.n + Cc];  // design-matrix column (MeanParameters.scala:55-65)
     } else if (rclass == 3) {
       v = cy[cl] - cm[cl];  // GaussianProcess.scala:120-122
     } else {
@@ -121,9 +124,9 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
 
 void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
                   const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
-                  int full) {
+                  int full, const double* rows) {
   dim3 grid(g.rt * g.nt, g.batch);
-  k_build<<<grid, 256, 0, st>>>(g, x, y, xstar, hyper, nugget, mats, mode, full);
+  k_build<<<grid, 256, 0, st>>>(g, x, y, xstar, hyper, nugget, mats, mode, full, rows);
 }
 
 }  // namespace gpb

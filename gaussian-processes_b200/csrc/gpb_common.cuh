@@ -25,10 +25,11 @@ struct Hyper {
 
 // Geometry of one (batched) tall lower-trapezoidal system:
 //   rows  0 .. npad-1           training points (identity-padded to a multiple of TILE)
-//   rows  npad .. npad+apad-1   appended rows: m test points (K* rows), then one rhs row (y - m(x))
+//   rows  npad .. npad+apad-1   appended rows: m test points (K* rows), `design` explicit rows, then one rhs row (y - m(x))
 // stored column-major, leading dimension ld = npad + apad, npad columns, one matrix per proposal.
 struct Geom {
   int n, dim, m;        // training size, input dimension, number of test points
+  int design;           // explicit appended rows (design-matrix columns) between the test rows and the rhs row
   int npad, apad, ld;   // padded sizes
   int nt, rt;           // tile columns (npad/TILE), tile rows (ld/TILE)
   int rhs_row;          // absolute row index of the rhs row (npad + m)

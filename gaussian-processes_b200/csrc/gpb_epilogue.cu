@@ -74,6 +74,90 @@ k_pred_epilogue(Geom g, const double* __restrict__ mats, const Hyper* __restrict
   }
 }
 
+// Gibbs step of the plane mean (MeanParameters.samplePlane, MeanParameters.scala:74-103): with the
+// design-matrix columns X_a carried through the panel solves as appended rows V_a = X_a^T L^-T,
+//   X^T K^-1 X = V V^T   and   X^T u  (u = L^-1 y, the reference multiplies X^T by u, :94)
+// are d*(d+1)/2 + d reductions over n.  out: G [d*d] (symmetric, row-major) then w [d].
+__global__ void __launch_bounds__(256)
+k_plane_epilogue(Geom g, const double* __restrict__ mats, const double* __restrict__ rows,
+                 double* __restrict__ out) {
+  constexpr int MAXD = 4;
+  const int d = g.design;
+  double G[MAXD][MAXD], w[MAXD];
+#pragma unroll
+  for (int a = 0; a < MAXD; ++a) { w[a] = 0.0;
+#pragma unroll
+    for (int b = 0; b < MAXD; ++b) G[a][b] = 0.0; }
+  const size_t r0 = (size_t)g.npad + g.m;
+  for (int c = threadIdx.x; c < g.n; c += blockDim.x) {
+    const double* col = mats + (size_t)c * g.ld;
+    const double u = col[g.rhs_row];
+    double v[MAXD];
+#pragma unroll
+    for (int a = 0; a < MAXD; ++a) v[a] = (a < d) ? col[r0 + a] : 0.0;
+#pragma unroll
+    for (int a = 0; a < MAXD; ++a) {
+      if (a < d) w[a] = fma(rows[(size_t)a * g.n + c], u, w[a]);
+#pragma unroll
+      for (int b = a; b < MAXD; ++b) G[a][b] = fma(v[a], v[b], G[a][b]);
+    }
+  }
+  __shared__ double red[8][MAXD * MAXD + MAXD];
+  const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int a = 0; a < MAXD; ++a) {
+    const double ws = warp_sum(w[a]);
+    if (lane == 0) red[wid][MAXD * MAXD + a] = ws;
+#pragma unroll
+    for (int b = a; b < MAXD; ++b) {
+      const double gs = warp_sum(G[a][b]);
+      if (lane == 0) red[wid][a * MAXD + b] = gs;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int a = 0; a < d; ++a) {
+      for (int b = a; b < d; ++b) {
+        double t = 0.0;
+        for (int i = 0; i < 8; ++i) t += red[i][a * MAXD + b];
+        out[a * d + b] = t; out[b * d + a] = t;
+      }
+      double t = 0.0;
+      for (int i = 0; i < 8; ++i) t += red[i][MAXD * MAXD + a];
+      out[d * d + a] = t;
+    }
+  }
+}
+void launch_plane_epilogue(cudaStream_t st, const Geom& g, const double* mats, const double* rows,
+                           double* out) {
+  k_plane_epilogue<<<1, 256, 0, st>>>(g, mats, rows, out);
+}
+
+// GaussianProcess.draw (GaussianProcess.scala:67-83) with the Cholesky root: out = mu + L z, one
+// thread per row, columns ascending (coalesced along rows of the column-major factor).
+__global__ void __launch_bounds__(128)
+k_draw(Geom g, const double* __restrict__ mats, const double* __restrict__ z,
+       const double* __restrict__ mu, double* __restrict__ out) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ double zs[128];
+  double acc = 0.0;
+  const int cmax = min(g.n, (int)(blockIdx.x + 1) * (int)blockDim.x);
+  for (int c0 = 0; c0 < cmax; c0 += 128) {
+    __syncthreads();
+    if (c0 + threadIdx.x < g.n) zs[threadIdx.x] = z[c0 + threadIdx.x];
+    __syncthreads();
+    if (r < g.n) {
+      const int cend = min(128, r + 1 - c0);
+      for (int c = 0; c < cend; ++c) acc = fma(mats[(size_t)(c0 + c) * g.ld + r], zs[c], acc);
+    }
+  }
+  if (r < g.n) out[r] = mu[r] + acc;
+}
+void launch_draw(cudaStream_t st, const Geom& g, const double* mats, const double* z, const double* mu,
+                 double* out) {
+  k_draw<<<(g.n + 127) / 128, 128, 0, st>>>(g, mats, z, mu, out);
+}
+
 __global__ void k_zero_upper(Geom g, double* __restrict__ mats) {
   const int c = blockIdx.x;
   double* col = mats + (size_t)blockIdx.y * g.mat_stride + (size_t)c * g.ld;

@@ -12,7 +12,7 @@ struct SchedState {
 
 void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
                   const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
-                  int full);
+                  int full, const double* rows = nullptr);
 
 // Tile Cholesky + panel solves of the tall system (gpb_chol.cu).
 //   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final)
@@ -34,6 +34,12 @@ size_t chol_linvt_doubles(const Geom& g);
 // Likelihood reductions Q, U1, S per proposal (gpb_epilogue.cu).
 void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, const int* info,
                         gpb_ll* out);
+// Plane-mean Gibbs statistics: G = V V^T over the solved design rows, w = X^T u (gpb_epilogue.cu).
+void launch_plane_epilogue(cudaStream_t st, const Geom& g, const double* mats, const double* rows,
+                           double* out /* [design*design + design] */);
+// mu + L z for a factored matrix (GaussianProcess.draw), one CTA per 64 rows.
+void launch_draw(cudaStream_t st, const Geom& g, const double* mats, const double* z, const double* mu,
+                 double* out);
 // Predictive mean / variance per test point.
 void launch_pred_epilogue(cudaStream_t st, const Geom& g, const double* mats, const Hyper* hyper,
                           double* mean, double* var);

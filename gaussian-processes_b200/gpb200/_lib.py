@@ -21,6 +21,7 @@ EXPORTS = [
     "gpb_build_cov", "gpb_potrf", "gpb_trsm_lower", "gpb_trsm_upper", "gpb_mh_run",
     "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
     "gpb_last_timing", "gpb_set_sched", "gpb_set_trace", "gpb_get_trace", "gpb_version",
+    "gpb_plane_stats", "gpb_sample_plane", "gpb_draw",
 ]
 
 
@@ -88,6 +89,12 @@ def load():
     L.gpb_mh_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Term), C.c_int,
                              _dp, C.c_int, _dp, C.POINTER(MhOpts), _dp, _dp, _dp, _dp, _ip, _ip]
     L.gpb_philox_streams.argtypes = [C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_plane_stats.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
+                                  _dp, _dp, _dp, _ip]
+    L.gpb_sample_plane.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
+                                   _dp, C.c_double, C.c_double, _dp, _dp, _ip]
+    L.gpb_draw.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, C.POINTER(Term), C.c_int, C.c_double,
+                           _dp, _dp, _dp, _ip]
     L.gpb_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     L.gpb_set_sched.argtypes = [C.c_void_p, C.c_int]
     L.gpb_set_trace.argtypes = [C.c_void_p, C.c_int]
@@ -218,6 +225,20 @@ class Context:
         out = b.T.copy()
         return out[:, 0] if vec else out
 
+    def draw(self, x, terms, z, mu=None, nugget=1e-3):
+        """gpb_draw: mu + L z with K + nugget I = L L^T.  Returns (sample, info)."""
+        xs, dim = x_soa(x)
+        n = xs.shape[1]
+        arr, nterms = terms_array([terms])
+        zv = as_f64(z)
+        muv = as_f64(mu) if mu is not None else None
+        out = np.empty(n)
+        info = C.c_int(0)
+        self._check(self.L.gpb_draw(self.h, n, dim, _ptr(xs), arr, nterms, float(nugget),
+                                    _ptr(muv) if muv is not None else None, _ptr(zv), _ptr(out),
+                                    C.byref(info)))
+        return out, info.value
+
     def trsm_lower(self, L, B):
         return self._trsm(self.L.gpb_trsm_lower, L, B)
 
@@ -282,6 +303,32 @@ class Dataset:
                                      _ptr(mean), _ptr(var), C.byref(info)))
         return mean, var, info.value
 
+
+    def plane_stats(self, terms, X, nugget=1e-6):
+        """gpb_plane_stats: X (n, d) design matrix -> (G = X^T K^-1 X, w = X^T L^-1 y, info)."""
+        ctx = self.ctx
+        arr, nterms = terms_array([terms])
+        Xc = np.ascontiguousarray(np.asarray(X, dtype=np.float64).T)   # [d][n]
+        d = Xc.shape[0]
+        G = np.empty((d, d)); w = np.empty(d)
+        info = C.c_int(0)
+        ctx._check(ctx.L.gpb_plane_stats(ctx.h, self.h, arr, nterms, float(nugget), d, _ptr(Xc),
+                                         _ptr(G), _ptr(w), C.byref(info)))
+        return G, w, info.value
+
+    def sample_plane(self, terms, X, prior_mean, prior_var, z, nugget=1e-6):
+        """gpb_sample_plane: one Gibbs draw of the plane coefficients.  Returns (beta, info)."""
+        ctx = self.ctx
+        arr, nterms = terms_array([terms])
+        Xc = np.ascontiguousarray(np.asarray(X, dtype=np.float64).T)
+        d = Xc.shape[0]
+        zv = as_f64(z)
+        beta = np.empty(d)
+        info = C.c_int(0)
+        ctx._check(ctx.L.gpb_sample_plane(ctx.h, self.h, arr, nterms, float(nugget), d, _ptr(Xc),
+                                          float(prior_mean), float(prior_var), _ptr(zv), _ptr(beta),
+                                          C.byref(info)))
+        return beta, info.value
 
     def mh_run(self, init_term_lists, ig, delta, z, u, beta=(), nugget=1e-3,
                formula=FORMULA_AS_PARSED, on_notpd=0):

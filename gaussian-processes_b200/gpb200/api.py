@@ -186,13 +186,43 @@ class MeanParameters:
         return Zero if p is Zero else Plane(pActual)
 
     @staticmethod
+    def makeDesignMatrix(xs):
+        """MeanParameters.scala:55-65, including its layout: `new DenseMatrix(n, m, xs.flatten)`
+        reads the row-major flattened coordinates column-major (interleaved columns for Two)."""
+        x = _pack_locations(xs)
+        if x.ndim == 1:
+            x = x[:, None]
+        n, m = x.shape
+        res = x.reshape(-1).reshape((m, n)).T
+        return np.hstack([np.ones((n, 1)), res])
+
+    @staticmethod
+    def samplePlane(prior, obs, xs, dist, p, rng=None):
+        """MeanParameters.scala:74-103 -> gpb_sample_plane (build + Cholesky + the design-matrix and
+        observation rows solved in the same pass on the device; the (dim+1)^2 algebra on the host)."""
+        _require_euclidean(dist)
+        if len(xs) != len(obs):
+            raise Exception("Dimension mismatch")  # Breeze: kxx is |xs| x |xs|, y has |obs| entries
+        rng = np.random.default_rng() if rng is None else rng
+        X = MeanParameters.makeDesignMatrix(xs)
+        ds = default_context().dataset(_pack_locations(xs), np.array([d.y for d in obs], dtype=np.float64))
+        try:
+            z = rng.standard_normal(X.shape[1])
+            beta, info = ds.sample_plane(_terms(p.kernelParameters), X, prior.mean, prior.variance, z,
+                                         nugget=1e-6)
+        finally:
+            ds.close()
+        if info != 0:
+            raise NotConvergedException(info)
+        return Plane(beta)
+
+    @staticmethod
     def sample(ys, xs, dist, prior):
-        """MeanParameters.scala:111-121.  Zero => identity.  Plane => samplePlane is SURVEY.md 8f
-        'next' #1 and is not built yet."""
-        def step(p):
+        """MeanParameters.scala:111-121.  Zero => identity.  Plane => Gibbs step samplePlane."""
+        def step(p, rng=None):
             if p.meanParameters is Zero:
                 return p
-            raise NotImplementedError("MeanParameters.samplePlane (SURVEY.md 8f-1) is not built yet")
+            return p.copy(meanParameters=MeanParameters.samplePlane(prior, ys, xs, dist, p, rng))
         return step
 
 
@@ -356,6 +386,20 @@ class GaussianProcess:
         return default_context().distance_matrix(_pack_locations(xs))
 
     @staticmethod
+    def draw(xs, dist, p, rng=None):
+        """GaussianProcess.scala:67-83 -> gpb_draw: mu + root z, nugget 1e-3.  Cholesky root instead
+        of the reference's eigSym root: equal in distribution, not bitwise."""
+        _require_euclidean(dist)
+        rng = np.random.default_rng() if rng is None else rng
+        x = _pack_locations(xs)
+        mf = MeanFunction.apply(p.meanParameters)
+        mu = np.array([mf(loc) for loc in xs], dtype=np.float64)
+        out, info = default_context().draw(x, _terms(p.kernelParameters), rng.standard_normal(len(xs)), mu, nugget=1e-3)
+        if info != 0:
+            raise NotConvergedException(info)
+        return out
+
+    @staticmethod
     def loglikelihood(observed, dist):
         """GaussianProcess.scala:109-127.  Curried like the reference: the observations are
         uploaded when the outer function is applied; the returned closure ships only the
@@ -494,6 +538,6 @@ class Mcmc:
             p = initP
             while True:
                 yield p
-                p = kern_step(mean_step(p), rng)
+                p = kern_step(mean_step(p, rng), rng)
 
         return chain()

@@ -53,3 +53,45 @@ def run_sharded(total_chains, iters, P, seed, runner, dist=None, device=None):
         parts.append(o.cpu().numpy()[:, :c])
     full = np.concatenate(parts, axis=1)
     return full[..., :P], full[..., P], full[..., P + 1].astype(np.int32)
+
+
+# ---- chain files -----------------------------------------------------------
+def param_names(terms, nbeta=0):
+    """Column names in the order the examples' `format` writes them (SimulatedGp.scala:159-160):
+    kernelParameters.flatMap(_.toList) ::: meanParameters.toList."""
+    names, se, wh = [], 0, 0
+    for t in terms:
+        kind = t[0]
+        if kind in (0, "se"):
+            sfx = "" if se == 0 else f"_{se}"
+            names += [f"h{sfx}", f"sigma{sfx}"]; se += 1
+        else:
+            names.append("sigma_y" if wh == 0 else f"sigma_y_{wh}"); wh += 1
+    return names + [f"beta_{i}" for i in range(nbeta)]
+
+
+def write_chains(prefix, states, names, chain0=0):
+    """One CSV per chain, `${prefix}_${chain}.csv` (Streaming.writeParallelChain's naming, read back
+    at SimulatedGp.scala:209-219 with a header row): header = parameter names, one row per
+    iteration.  states: (iters, chains, P) as gathered from the devices.  Returns the paths."""
+    states = np.asarray(states, dtype=np.float64)
+    iters, chains, P = states.shape
+    if len(names) != P:
+        raise ValueError("one column name per parameter")
+    paths = []
+    for c in range(chains):
+        path = f"{prefix}_{chain0 + c}.csv"
+        with open(path, "w") as f:
+            f.write(",".join(names) + "\n")
+            for it in range(iters):
+                f.write(",".join(repr(float(v)) for v in states[it, c]) + "\n")
+        paths.append(path)
+    return paths
+
+
+def read_chain(path):
+    """Read a chain file back: (names, (iters, P) array); values round-trip exactly (repr)."""
+    with open(path) as f:
+        names = f.readline().strip().split(",")
+        rows = [[float(v) for v in line.split(",")] for line in f if line.strip()]
+    return names, np.array(rows, dtype=np.float64).reshape(-1, len(names))

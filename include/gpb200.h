@@ -143,6 +143,26 @@ int gpb_mh_run(gpb_ctx *ctx, const gpb_dataset *ds, int chains, int iters, const
 int gpb_philox_streams(unsigned long long seed, int chain0, int chains, int iters, int P, double *z,
                        double *uu);
 
+/* ---- "next" rows of the scope table ------------------------------------------ */
+/* MeanParameters.samplePlane(prior, obs, xs, dist, p)  MeanParameters.scala:74-103, the Gibbs step
+ * of the plane mean in Mcmc.sample (Mcmc.scala:73).  X: the d = dim+1 design-matrix columns
+ * [d][n] exactly as makeDesignMatrix lays them out (MeanParameters.scala:55-65; the caller keeps its
+ * layout quirk).  They ride the factorisation as appended rows, so X^T K^-1 X = V V^T needs no
+ * back-solve.  gpb_plane_stats returns G = X^T (K + nugget I)^-1 X [d*d] and w = X^T L^-1 y [d];
+ * gpb_sample_plane finishes the d x d algebra on the host: prec = G + I/var, mean = prec \
+ * (mean0/var + w), beta = mean + chol(prec) \ z with z the d standard normals the reference draws.
+ * nugget is 1e-6 in the reference (:84). */
+int gpb_plane_stats(gpb_ctx *ctx, const gpb_dataset *ds, const gpb_term *terms, int nterms,
+                    double nugget, int d, const double *X, double *G, double *w, int *info);
+int gpb_sample_plane(gpb_ctx *ctx, const gpb_dataset *ds, const gpb_term *terms, int nterms,
+                     double nugget, int d, const double *X, double prior_mean, double prior_var,
+                     const double *z, double *beta, int *info);
+/* GaussianProcess.draw(xs, dist, p)  GaussianProcess.scala:67-83: mu + root z with nugget 1e-3.
+ * The reference takes the symmetric eigen root (eigSym); this uses the Cholesky root of the same
+ * covariance -- equal in distribution, not bitwise.  mu may be NULL (Zero mean). */
+int gpb_draw(gpb_ctx *ctx, int n, int dim, const double *x, const gpb_term *terms, int nterms,
+             double nugget, const double *mu, const double *z, double *out, int *info);
+
 /* ---- misc -------------------------------------------------------------------------------- */
 const char *gpb_strerror(int status);
 const char *gpb_last_cuda_error(const gpb_ctx *ctx);

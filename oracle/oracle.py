@@ -192,3 +192,49 @@ def mh_run(x, y, init_terms, ig, delta, z, u, beta=(), nugget=1e-3, formula=0, e
                           states.ctypes.data_as(_dp), ll.ctypes.data_as(_dp),
                           acc.ctypes.data_as(_ip))
     return states, ll, acc, rc
+
+
+# ---- "next" rows of the scope table: numpy restatements, small cases only -------
+def design_matrix(x):
+    """MeanParameters.makeDesignMatrix (MeanParameters.scala:55-65), INCLUDING its layout quirk:
+    `new DenseMatrix(n, m, xs.flatten.toArray)` reads the row-major flattened coordinates as a
+    column-major n x m matrix, so for 2-D locations the coordinate columns are interleaved."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[:, None]
+    n, m = x.shape
+    res = x.reshape(-1).reshape((m, n)).T          # column-major view of the flattened data
+    return np.hstack([np.ones((n, 1)), res])
+
+
+def sample_plane(x, y, terms, prior_mean, prior_var, z, nugget=1e-6):
+    """MeanParameters.samplePlane (MeanParameters.scala:74-103), line by line; `\\` on a square
+    Breeze matrix is an LU solve (np.linalg.solve).  z: the standard normals of `Gaussian(0,1).draw`.
+    Returns (beta, prec, mean)."""
+    X = design_matrix(x)
+    K = build_cov(x, terms, nugget)
+    L, _info = potrf_lower(K)
+    m = X.shape[1]
+    prior_prec = np.eye(m) / prior_var
+    prec = X.T @ np.linalg.solve(K, X) + prior_prec
+    u = trsv_lower(L, np.asarray(y, dtype=np.float64))
+    mean = np.linalg.solve(prec, prior_prec @ np.full(m, float(prior_mean)) + X.T @ u)
+    root = np.linalg.cholesky(prec)
+    beta = mean + np.linalg.solve(root, np.asarray(z, dtype=np.float64))
+    return beta, prec, mean
+
+
+def draw(x, terms, z, beta=(), nugget=1e-3):
+    """GaussianProcess.draw (GaussianProcess.scala:67-83): mu + V sqrt(Lambda) z from eigSym.  The
+    device path uses mu + L z (Cholesky): equal in distribution, not bitwise, so
+    tests compare covariances / the Cholesky form, which this also returns."""
+    xx = np.asarray(x, dtype=np.float64)
+    if xx.ndim == 1:
+        xx = xx[:, None]
+    K = build_cov(x, terms, nugget)
+    mu = np.zeros(len(xx))
+    if len(beta):
+        mu = beta[0] + xx @ np.asarray(beta[1:], dtype=np.float64)
+    w, V = np.linalg.eigh(K)
+    zz = np.asarray(z, dtype=np.float64)
+    return mu + V @ (np.sqrt(w) * zz), mu + potrf_lower(K)[0] @ zz

@@ -118,3 +118,26 @@ def test_params_array_round_trip(terms, beta):
         flat.extend(t[1:])
     assert list(arr) == flat
     assert KernelParameters.arrayToParams(p, arr) == p
+
+
+def test_chain_files_round_trip(tmp_path):
+    """`${prefix}_${chain}.csv`, header of parameter names, one row per iteration."""
+    import numpy as np
+    from gpb200 import chains as CH
+    names = CH.param_names([(0, 1.0, 1.0), (0, 1.0, 1.0), (1, 1.0, 0.0)], nbeta=2)
+    assert names == ["h", "sigma", "h_1", "sigma_1", "sigma_y", "beta_0", "beta_1"]
+    st = np.random.default_rng(0).standard_normal((5, 3, 3))
+    paths = CH.write_chains(str(tmp_path / "gpmcmc"), st, ["h", "sigma", "sigma_y"], chain0=4)
+    assert [p.rsplit("_", 1)[1] for p in paths] == ["4.csv", "5.csv", "6.csv"]
+    nm, back = CH.read_chain(paths[1])
+    assert nm == ["h", "sigma", "sigma_y"] and np.array_equal(back, st[:, 1])
+
+
+def test_design_matrix_mirrors_the_reference_layout():
+    """MeanParameters.makeDesignMatrix flattens row-major and reads column-major (MeanParameters.scala:62)."""
+    import numpy as np
+    from gpb200 import api as gp
+    X = gp.MeanParameters.makeDesignMatrix([gp.Two(1.0, 2.0), gp.Two(3.0, 4.0), gp.Two(5.0, 6.0)])
+    assert np.array_equal(X, np.array([[1, 1, 4], [1, 2, 5], [1, 3, 6.0]]))
+    X1 = gp.MeanParameters.makeDesignMatrix([gp.One(7.0), gp.One(8.0)])
+    assert np.array_equal(X1, np.array([[1, 7], [1, 8.0]]))

@@ -391,3 +391,33 @@ def test_full_size_c4_n32768_predictive_10k(ctx):
     assert np.allclose(mean, mean_t, rtol=1e-7, atol=1e-8)
     assert np.allclose(var, var_t, rtol=1e-7, atol=1e-8)
     ds.close()
+
+
+@pytest.mark.parametrize("n,dim", [(40, 1), (300, 2), (1000, 2)])
+def test_sample_plane_parity(ctx, oracle, n, dim):
+    """MeanParameters.samplePlane through the C ABI vs the numpy restatement."""
+    rng = np.random.default_rng(50 + n)
+    x = rng.uniform(-10, 10, size=(n, dim))
+    y = 0.7 + 0.2 * x[:, 0] + rng.standard_normal(n)
+    X = oracle.design_matrix(x)
+    z = rng.standard_normal(dim + 1)
+    beta_o, prec_o, mean_o = oracle.sample_plane(x, y, SE_W, 1.0, 4.0, z, nugget=1e-6)
+    ds = ctx.dataset(x, y)
+    G, w, info = ds.plane_stats(gterms(SE_W), X, nugget=1e-6)
+    assert info == 0
+    assert np.allclose(G + np.eye(dim + 1) / 4.0, prec_o, rtol=1e-9)
+    beta, info = ds.sample_plane(gterms(SE_W), X, 1.0, 4.0, z, nugget=1e-6)
+    assert info == 0 and np.allclose(beta, beta_o, rtol=1e-8, atol=1e-10)
+    ds.close()
+
+
+def test_draw_uses_the_cholesky_root(ctx, oracle):
+    """GaussianProcess.draw = mu + root z; the device root is the Cholesky factor."""
+    rng = np.random.default_rng(61)
+    n = 500
+    x = np.sort(rng.uniform(-10, 10, n))
+    z = rng.standard_normal(n)
+    mu = 0.5 + 0.1 * x
+    out, info = ctx.draw(x, gterms(SE_W), z, mu, nugget=1e-3)
+    _, chol_draw = oracle.draw(x, SE_W, z, beta=(0.5, 0.1), nugget=1e-3)
+    assert info == 0 and np.allclose(out, chol_draw, rtol=1e-9, atol=1e-11)

@@ -167,3 +167,30 @@ def test_inverse_gamma_prior(oracle):
     p = oracle.prior(SE_W, ig)
     f = oracle.lib().orc_invgamma_logpdf
     assert p == (0.0 + (f(3.0, 4.0, 3.0) + f(3.0, 6.0, 5.5))) + f(10.0, 6.0, 0.5)
+
+
+def test_sample_plane_and_draw_restatements(oracle):
+    """SURVEY.md 8f-1/-3 restatements: the Gibbs draw solves the stated normal equations; the
+    design matrix keeps the reference's layout; both roots of `draw` reproduce K."""
+    rng = np.random.default_rng(12)
+    x = rng.uniform(-5, 5, size=(40, 2)); y = rng.standard_normal(40)
+    terms = [("se", 3.0, 5.5), ("white", 0.5)]
+    z = rng.standard_normal(3)
+    beta, prec, mean = oracle.sample_plane(x, y, terms, 1.0, 2.0, z)
+    X = oracle.design_matrix(x)
+    assert np.array_equal(X[:, 1], x.reshape(-1)[:40])          # interleaved, as the reference builds it
+    K = oracle.build_cov(x, terms, 1e-6)
+    assert np.allclose(prec, X.T @ np.linalg.solve(K, X) + np.eye(3) / 2.0, rtol=1e-10)
+    L = np.linalg.cholesky(prec)
+    assert np.allclose(L @ (beta - mean), z, rtol=1e-9, atol=1e-12)
+    x1 = np.sort(rng.uniform(-10, 10, 50))
+    ze = rng.standard_normal(50)
+    eig_draw, chol_draw = oracle.draw(x1, terms, ze, beta=(0.5, 0.1))
+    K1 = oracle.build_cov(x1, terms, 1e-3)
+    mu = 0.5 + 0.1 * x1
+    Lc = np.linalg.cholesky(K1)
+    assert np.allclose(chol_draw, mu + Lc @ ze, rtol=1e-10, atol=1e-12)
+    w, V = np.linalg.eigh(K1)
+    R = V * np.sqrt(w)
+    assert np.allclose(R @ R.T, Lc @ Lc.T, rtol=1e-9, atol=1e-10)   # two roots of the same covariance
+    assert np.allclose(eig_draw, mu + R @ ze, rtol=1e-8, atol=1e-10)

@@ -22,6 +22,7 @@
 // Roofline: trailing contraction n^3/3 flop on the FP64 tensor pipe (37.1 TFLOP/s measured DMMA
 // issue peak on this B200, profiles/r01_dmma_shapes_microbench.log).
 #include <cuda.h>
+#include <cstdlib>
 
 #include "gpb_internal.h"
 
@@ -378,8 +379,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
 #pragma unroll 1
           for (int s = 0; s < TILE / KC; ++s) {
             if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
-            mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
             const int col = kc * TILE + s * KC;
+            mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
             tma_load_3d(&sm.stage[stage][0], &tmap, d.j * TILE, col, d.b, &sm.full[stage]);
             tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col, d.b, &sm.full[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }

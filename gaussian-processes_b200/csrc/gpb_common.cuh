@@ -157,7 +157,10 @@ __device__ __forceinline__ double2 ld_cg2(const double* p) {
 // ---- FP64 tensor core: D(8x8) += A(8x4) * B(4x8), SASS DMMA.8x8x4 ------------------------------
 // lane = 4*g + t:  a = A[row g][k t],  b = B[k t][col g],  c0/c1 = C[row g][col 2t], [col 2t+1]
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+#ifndef GPB_DMMA_ASM
+#define GPB_DMMA_ASM asm volatile
+#endif
+  GPB_DMMA_ASM("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
 }

@@ -43,7 +43,14 @@ namespace gpb {
 constexpr int KC = GPB_KC;             // panel columns per pipeline stage
 constexpr int STAGES = GPB_STAGES;
 constexpr int CTAS_PER_SM = GPB_CTAS_PER_SM;  // co-resident CTAs: one factors/solves while the other contracts
-constexpr int NCONS = 128;             // consumer threads: 4 warps, 32x32 sub-tile each
+#ifndef GPB_CONS_WARPS
+#define GPB_CONS_WARPS 4
+#endif
+constexpr int CW = GPB_CONS_WARPS;     // consumer warps per CTA: 4 (32 x 32 sub-tiles) or 8 (32 c x 16 r)
+static_assert(CW == 4 || CW == 8, "consumer warps");
+constexpr int NCONS = 32 * CW;         // consumer threads
+constexpr int RW = TILE / (CW / 2);    // tile rows r per consumer warp in the contraction
+constexpr int NTW = RW / 8;            // 8-row fragments per warp
 constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
 constexpr int STAGE_DOUBLES = 2 * KC * LDT;
 constexpr int SCOLS = 2 * KC;          // tile columns (of L_jj^-T, or of the diagonal scratch) one stage holds
@@ -179,8 +186,8 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
     const int c = e >> 6, k = e & (TILE - 1);
     wcol(sm, s0, c)[k] = (c == k) ? 1.0 : 0.0;
   }
-  const bool top = tid < TILE;
-  const int rr = top ? tid : tid - TILE;   // entry (R, c): top Cs[c * LDT + rr], bottom wcol(c)[rr]
+  const bool top = tid < TILE, act = tid < 2 * TILE;   // threads beyond the 128 stacked rows only keep the barriers
+  const int rr = top ? tid : (tid - TILE) & (TILE - 1);  // entry (R, c): top Cs[c * LDT + rr], bottom wcol(c)[rr]
   bar_named(1, NCONS);
 #pragma unroll 1
   for (int c0 = 0; c0 < TILE; c0 += PB) {
@@ -188,6 +195,9 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
     if (top) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) p[q] = sm.Cs[(c0 + q) * LDT + rr];
+    } else if (!act) {
+#pragma unroll
+      for (int q = 0; q < PB; ++q) p[q] = 0.0;
     } else {
 #pragma unroll
       for (int q = 0; q < PB; ++q) p[q] = wcol(sm, s0, c0 + q)[rr];
@@ -195,7 +205,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
 #pragma unroll
     for (int q = 0; q < PB; ++q) {
       double* cb = sm.colbuf[q & 1];
-      cb[tid] = p[q];
+      if (act) cb[tid] = p[q];
       bar_named(1, NCONS);
       const double a = cb[c0 + q];                 // pivot (Schur complement diagonal)
       if (tid == c0 + q && !(a > 0.0) && sm.bad_col < 0) sm.bad_col = c0 + q;  // first bad column
@@ -211,7 +221,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
     if (top) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) sm.Cs[(c0 + q) * LDT + rr] = p[q];
-    } else {
+    } else if (act) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) wcol(sm, s0, c0 + q)[rr] = p[q];
     }
@@ -220,8 +230,8 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
     if (cN < TILE) {
       // M(R, c2) -= sum_q P(R, q) P(c2, q)  for c2 >= cN;  D[m = c2][n = R], k = q
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        const int blk = 2 * warp + h;              // live row block 0..7
+      for (int h = 0; h < 8 / CW; ++h) {
+        const int blk = (8 / CW) * warp + h;       // live row block 0..7
         const int ntop = (TILE - cN) / 8;          // live top blocks: rows cN .. 63
         const bool btop = blk < ntop;
         const int r0 = btop ? cN + 8 * blk : 8 * (blk - ntop);
@@ -249,7 +259,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
   {
     const int r = tid & (TILE - 1), half = tid >> 6;
 #pragma unroll 4
-    for (int c = half; c < TILE; c += 2) {
+    for (int c = half; c < TILE; c += NCONS / TILE) {
       if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
       LT[c * LDT + r] = (c >= r) ? wcol(sm, s0, c)[r] : 0.0;
     }
@@ -259,7 +269,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
 // Triangular-solve mode: sm.Cs holds a given lower-triangular L_jj; thread 64+k computes row k of
 // L_jj^-T by substitution on the stacked [L; I] (no factorisation, no barriers: L is read-only).
 __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT, int tid) {
-  if (tid < TILE) return;
+  if (tid < TILE || tid >= 2 * TILE) return;
   const int k = tid - TILE;
   double row[TILE];
 #pragma unroll
@@ -425,7 +435,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
 
   // ================================= consumer warps =================================
   const int gq = lane >> 2, tq = lane & 3;          // DMMA fragment coordinates
-  const int wc = warp >> 1, wr = warp & 1;          // warp's 32x32 sub-tile: c block, r block
+  const int wc = warp / (CW / 2), wr = warp % (CW / 2);   // warp's sub-tile: 32 columns c x RW rows r
   int q = 0, relc = 0;
   // post (counter, value) for the producer lane to publish; all consumer stores are issued
   auto post_release = [&](int* ptr, int val) {
@@ -458,13 +468,13 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       continue;
     }
 
-    // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*32 + nt*8 + 2*tq + {0,1}
-    double acc[4][4][2];
+    // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*RW + nt*8 + 2*tq + {0,1}
+    double acc[4][NTW][2];
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
+      for (int nt = 0; nt < NTW; ++nt) {
+        const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
         double2 v = ld_cg2(Aij + (size_t)c * g.ld + r);
         acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
       }
@@ -483,17 +493,17 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       ++not_ready;
       if (!mbar_wait(&sm.full[st], ph)) atomicExch(&sched->error, 5);
     };
-    auto load_frag = [&](const double* P, int ks, double (&a)[4], double (&bb)[4]) {
+    auto load_frag = [&](const double* P, int ks, double (&a)[4], double (&bb)[NTW]) {
       const int k = ks * 4 + tq;
 #pragma unroll
       for (int mt = 0; mt < 4; ++mt) a[mt] = -P[k * LDT + wc * 32 + mt * 8 + gq];
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt) bb[nt] = P[(KC + k) * LDT + wr * 32 + nt * 8 + gq];
+      for (int nt = 0; nt < NTW; ++nt) bb[nt] = P[(KC + k) * LDT + wr * RW + nt * 8 + gq];
     };
     if (nstage > 0) {
       wait_full(stage, phase);
       if (tr) tr[2] = clock64();
-      double a[4], bb[4];
+      double a[4], bb[NTW];
       load_frag(&sm.stage[stage][0], 0, a, bb);
 #pragma unroll 1
       for (int it = 0; it < nstage; ++it) {
@@ -504,7 +514,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         for (int ks = 0; ks < KC / 4; ++ks) {
           // fragments of the next k-step (or of the next stage's first k-step) are fetched before
           // this step's 16 DMMAs issue, so neither the LDS latency nor the barrier probe is exposed
-          double an[4], bn[4];
+          double an[4], bn[NTW];
           if (ks + 1 < KC / 4) {
             load_frag(P, ks + 1, an, bn);
           } else if (it + 1 < nstage) {
@@ -512,14 +522,18 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             load_frag(&sm.stage[nst][0], 0, an, bn);
           } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { an[i] = 0.0; bn[i] = 0.0; }
+            for (int i = 0; i < 4; ++i) an[i] = 0.0;
+#pragma unroll
+            for (int i = 0; i < NTW; ++i) bn[i] = 0.0;
           }
 #pragma unroll
           for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-            for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+            for (int nt = 0; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { a[i] = an[i]; bb[i] = bn[i]; }
+          for (int i = 0; i < 4; ++i) a[i] = an[i];
+#pragma unroll
+          for (int i = 0; i < NTW; ++i) bb[i] = bn[i];
         }
         __syncwarp();
         if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
@@ -533,8 +547,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        const int c = wc * 32 + mt * 8 + gq, r = wr * 32 + nt * 8 + 2 * tq;
+      for (int nt = 0; nt < NTW; ++nt) {
+        const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
         *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
       }
     if (tid == 0) sm.bad_col = -1;
@@ -572,38 +586,41 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     } else {
       // ---------- off-diagonal task: X = C * L_jj^-T, L_jj^-T streamed through the ring ----------
-      // stage s carries rows c = s*SCOLS .. of L_jj^-T; each warp solves those columns of X for its
-      // 16 rows r and stores them straight to global memory
-      constexpr int CT = SCOLS / 8;
+      // stage s carries rows c = s*SCOLS .. of L_jj^-T; the warps solve those columns of X and store
+      // them straight to global memory
+      // warp w: rows r = (w % 4) * 16 .. +16, and the (w / 4)-th share of the stage's column tiles
+      constexpr int CT = SCOLS / 8;          // 8-column tiles of X per stage
+      constexpr int CTW = CT / (CW / 4);     // ... per warp
+      const int rq = warp & 3, ch = warp >> 2;
 #pragma unroll 1
       for (int s = 0; s < LT_STAGES; ++s) {
         wait_full(stage, phase);
         if (tr && s == 0) tr[4] = clock64();
-        const double* LTs = &sm.stage[stage][0];
-        double x[CT][2][2];
+        const double* LTs = &sm.stage[stage][ch * CTW * 8 * LDT];
+        double x[CTW][2][2];
 #pragma unroll
-        for (int ct = 0; ct < CT; ++ct)
+        for (int ct = 0; ct < CTW; ++ct)
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
-        const int kend = (s + 1) * SCOLS;   // L^-T(k, c) == 0 for k > c
+        const int kend = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
 #pragma unroll 2
         for (int k0 = 0; k0 < kend; k0 += 4) {
           const int k = k0 + tq;
-          double a[CT], bb[2];
+          double a[CTW], bb[2];
 #pragma unroll
-          for (int ct = 0; ct < CT; ++ct) a[ct] = LTs[(ct * 8 + gq) * LDT + k];
+          for (int ct = 0; ct < CTW; ++ct) a[ct] = LTs[(ct * 8 + gq) * LDT + k];
 #pragma unroll
-          for (int nt = 0; nt < 2; ++nt) bb[nt] = sm.Cs[k * LDT + warp * 16 + nt * 8 + gq];
+          for (int nt = 0; nt < 2; ++nt) bb[nt] = sm.Cs[k * LDT + rq * 16 + nt * 8 + gq];
 #pragma unroll
-          for (int ct = 0; ct < CT; ++ct)
+          for (int ct = 0; ct < CTW; ++ct)
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) dmma884(x[ct][nt][0], x[ct][nt][1], a[ct], bb[nt]);
         }
 #pragma unroll
-        for (int ct = 0; ct < CT; ++ct)
+        for (int ct = 0; ct < CTW; ++ct)
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) {
-            const int c = s * SCOLS + ct * 8 + gq, r = warp * 16 + nt * 8 + 2 * tq;
+            const int c = s * SCOLS + (ch * CTW + ct) * 8 + gq, r = rq * 16 + nt * 8 + 2 * tq;
             *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(x[ct][nt][0], x[ct][nt][1]);
           }
         // the stores above consumed every DMMA of this stage, so its LDS have completed
@@ -682,7 +699,18 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   int launches = 0;
   if (mode == 0) {
-    const long long slots = (long long)num_sms * CTAS_PER_SM;
+    // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; single small proposals
+    // are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA that
+    // has its SM to itself factors and solves about twice as fast (n=4096, one proposal: 1.66 ms
+    // vs 2.14 ms).  GPB_CTAS_PER_SM_RT overrides (tuning).
+    static int env_ctas = -1;
+    if (env_ctas < 0) { const char* e = getenv("GPB_CTAS_PER_SM_RT"); env_ctas = e ? atoi(e) : 0; }
+    // work-bound (contraction time at ~28 TFLOP/s) vs chain-bound (~25 us per block column)
+    const double work_us = (double)g.batch * g.npad * (double)g.npad * g.ld / 3.0 / 28e6;
+    const double chain_us = 25.0 * g.nt;
+    int ctas = (work_us >= chain_us) ? CTAS_PER_SM : 1;
+    if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
+    const long long slots = (long long)num_sms * ctas;
     int grid = (int)(total < slots ? total : slots);
     k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
                                                            (int)total, 0, solve_only, trace);

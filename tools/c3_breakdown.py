@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "gaussian-proces
 from gpb200 import _lib as G
 ctx = G.Context(0)
 rng = np.random.default_rng(3)
-for n, B in [(1024, 256), (1024, 32), (4096, 1), (4096, 8), (4096, 16), (8192, 8), (300, 256)]:
+for n, B in [(1024, 256), (1024, 32), (1024, 8), (1024, 1), (4096, 1), (4096, 2), (4096, 8), (8192, 1), (8192, 8), (300, 256), (300, 2)]:
     x = rng.uniform(-10, 10, size=(n, 2)); y = rng.standard_normal(n)
     ds = ctx.dataset(x, y)
     props = [[(0, 3.0 * math.exp(0.05 * rng.standard_normal()), 5.5), (1, 0.5, 0.0)] for _ in range(B)]

@@ -55,6 +55,9 @@ constexpr int NTHREADS = NCONS + 32;   // + 1 producer warp
 constexpr int STAGE_DOUBLES = 2 * KC * LDT;
 constexpr int SCOLS = 2 * KC;          // tile columns (of L_jj^-T, or of the diagonal scratch) one stage holds
 constexpr int LT_STAGES = TILE / SCOLS;  // stages that carry one 64 x 64 L_jj^-T tile
+constexpr int AT_STAGES = TILE / SCOLS;  // stages that carry the task's own tile (accumulator start)
+static_assert(SCOLS == 32 && AT_STAGES == 2, "each consumer warp's 32 columns of the tile sit in one stage");
+static_assert(STAGES >= AT_STAGES + 2, "ring too small");
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
 constexpr int TRACE_SLOTS = 10;
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
@@ -355,14 +358,17 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     int q = 0, static_next = task_begin + blockIdx.x;
     RelState rs; rs.r = 0;
     int posted = 0;   // tasks handed to the consumers that will post a publication
+    // the next ticket is drawn while the current task's last stages are still in flight (after its
+    // contraction stages are issued, before its solve stages), so the atomic's latency is hidden
+    auto fetch = [&]() {
+      int tn;
+      if (static_sched) { tn = static_next; static_next += gridDim.x; }
+      else tn = task_begin + atomicAdd(&sched->next_task, 1);
+      return tn >= task_end ? -1 : tn;
+    };
+    int t_next = (lane == 0) ? fetch() : 0;
     for (;;) {
-      int t;
-      if (lane == 0) {
-        if (static_sched) { t = static_next; static_next += gridDim.x; }
-        else t = task_begin + atomicAdd(&sched->next_task, 1);
-        if (t >= task_end) t = -1;
-      }
-      t = __shfl_sync(0xffffffffu, t, 0);
+      int t = __shfl_sync(0xffffffffu, t_next, 0);
       const int slot = q & 1, qpar = (q >> 1) & 1;
       if (lane == 0) {
         if (!mbar_wait_serving(&sm.tq_empty[slot], qpar ^ 1, sm, rs)) atomicExch(&sched->error, 2);
@@ -373,9 +379,23 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       if (t < 0) break;
       if (!solve_only) ++posted;
       const TaskDesc d = decode_task(g, t, jcache);
-      if (solve_only && d.i < g.nt) continue;  // L is given: no accumulation for top-square tiles
+      if (solve_only && d.i < g.nt) {          // L is given: no accumulation for top-square tiles
+        if (lane == 0) t_next = fetch();
+        continue;
+      }
       const int* done_b = done + (size_t)d.b * g.rt;
       if (lane == 0) {
+        // the tile itself (accumulator start value) comes first, as AT_STAGES ordinary stages:
+        // stage s holds tile columns s*SCOLS .. in [column][LDT] order
+#pragma unroll 1
+        for (int s = 0; s < AT_STAGES; ++s) {
+          if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+          mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+          const int col = d.j * TILE + s * SCOLS;
+          tma_load_3d(&sm.stage[stage][0], &tmap, d.i * TILE, col, d.b, &sm.full[stage]);
+          tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col + KC, d.b, &sm.full[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
         // one elected lane drives the ring: two TMA boxes per stage ({LDT rows x KC cols}: the
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
         // progress counters only grow: poll again only when the last value seen is not enough
@@ -396,6 +416,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
+        t_next = fetch();
         if (d.i != d.j) {
           // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
           // ring: LT_STAGES stages of SCOLS rows each, as soon as diag(j) is published
@@ -468,23 +489,6 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       continue;
     }
 
-    // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*RW + nt*8 + 2*tq + {0,1}
-    double acc[4][NTW][2];
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < NTW; ++nt) {
-        const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
-        double2 v = ld_cg2(Aij + (size_t)c * g.ld + r);
-        acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
-      }
-
-    const int nstage = (solve_only && d.i < g.nt) ? 0 : d.j * (TILE / KC);
-    // Stage release is DELAYED by one stage: ptxas schedules mbarrier.arrive right behind the last
-    // LDS of a stage without waiting for those loads to return, and with two CTAs per SM the
-    // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
-    // is being consumed guarantees every DMMA that read s has issued, i.e. its LDS completed.
-    int pend = -1;
     int not_ready = 0;
     // fast path: the stage is almost always there already (test_wait is a plain probe; try_wait
     // costs ~100 cycles even on a completed phase)
@@ -493,6 +497,50 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       ++not_ready;
       if (!mbar_wait(&sm.full[st], ph)) atomicExch(&sched->error, 5);
     };
+    // acc[mt][nt] holds D[m = c][n = r]:  c = wc*32 + mt*8 + gq,  r = wr*RW + nt*8 + 2*tq + {0,1}
+    double acc[4][NTW][2];
+    int pre0 = -1, pre1 = -1;   // ring stages that carried the tile; released once acc has been consumed
+    if (solve_only && d.i < g.nt) {
+      // given factor (diagonal tile of the triangular-solve mode): straight from global memory
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) {
+          const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+          double2 v = ld_cg2(Aij + (size_t)c * g.ld + r);
+          acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
+        }
+    } else {
+      pre0 = (int)stage;
+      wait_full(stage, phase);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      pre1 = (int)stage;
+      wait_full(stage, phase);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      if (tr) tr[2] = clock64();
+      const double* T = &sm.stage[wc == 0 ? pre0 : pre1][0];   // this warp's 32 tile columns
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) {
+          const double2 v = *reinterpret_cast<const double2*>(&T[(mt * 8 + gq) * LDT + wr * RW + nt * 8 + 2 * tq]);
+          acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
+        }
+    }
+    // release of the tile stages: only after something that needed acc has issued (LDS done)
+    auto release_pre = [&]() {
+      if (pre0 >= 0) {
+        if (lane == 0) { mbar_arrive(&sm.empty[pre0]); mbar_arrive(&sm.empty[pre1]); }
+        pre0 = pre1 = -1;
+      }
+    };
+
+    const int nstage = (solve_only && d.i < g.nt) ? 0 : d.j * (TILE / KC);
+    // Stage release is DELAYED by one stage: ptxas schedules mbarrier.arrive right behind the last
+    // LDS of a stage without waiting for those loads to return, and with two CTAs per SM the
+    // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
+    // is being consumed guarantees every DMMA that read s has issued, i.e. its LDS completed.
+    int pend = -1;
     auto load_frag = [&](const double* P, int ks, double (&a)[4], double (&bb)[NTW]) {
       const int k = ks * 4 + tq;
 #pragma unroll
@@ -502,7 +550,6 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     };
     if (nstage > 0) {
       wait_full(stage, phase);
-      if (tr) tr[2] = clock64();
       double a[4], bb[NTW];
       load_frag(&sm.stage[stage][0], 0, a, bb);
 #pragma unroll 1
@@ -536,6 +583,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           for (int i = 0; i < NTW; ++i) bb[i] = bn[i];
         }
         __syncwarp();
+        release_pre();
         if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
         pend = (int)stage;
         stage = nst; phase = nph;
@@ -553,6 +601,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       }
     if (tid == 0) sm.bad_col = -1;
     bar_named(1, NCONS);
+    release_pre();
     if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);  // accumulators are stored: all reads done
 
     if (d.i == d.j) {

@@ -89,9 +89,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
 
-    def stop(self):
+    def count_since(self, t):
+        return sum(1 for ts, _ in self.rows if ts >= t)
+
+    def stop(self, t0=None, t1=None, note="timed region"):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -100,7 +103,9 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for ts, r in self.rows:
+            if (t0 is not None and ts < t0) or (t1 is not None and ts > t1):
+                continue
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
@@ -109,7 +114,7 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "window": note}
 
 
 def cpu_evals(x, y, term_lists, threads):
@@ -170,6 +175,8 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- gpb200 has no CPU fallback")
     torch.cuda.set_device(local)
+    sampler = ClockSampler(local)
+    sampler.start()                 # nvidia-smi needs seconds to come up: start it before the set-up
     ctx = G.Context(local)
     x, y = make_dataset()
     ds = ctx.dataset(x, y)
@@ -195,9 +202,7 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step()
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
     l0 = ctx.launch_count()
     dev_ms, chol_ms = 0.0, 0.0
     t0 = time.perf_counter()
@@ -207,9 +212,23 @@ def run_ours(args):
         chol_ms += t[1]
         assert all(r.info == 0 for r in rs)
     barrier()
-    wall = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    wall = t1 - t0
     launches = ctx.launch_count() - l0
-    clocks = sampler.stop()
+    note = "timed region"
+    # a short timed region can fall between two 100 ms samples: then every rank keeps the same load
+    # running (untimed, same number of extra steps on all ranks: step() holds a collective) for
+    # ~0.6 s so that the sampler sees it, and the record says so
+    flag = torch.tensor([1.0 if sampler.count_since(t0) < 3 else 0.0, wall], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+    if float(flag[0]) > 0:
+        note = "same load continued after the timed region (timed region shorter than the sampling period)"
+        for _ in range(min(2000, int(0.6 / max(float(flag[1]) / args.steps, 1e-4)) + 1)):
+            step()
+        barrier()
+        t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1, note)
 
     # max over ranks of both clocks
     tt = torch.tensor([dev_ms, wall, chol_ms], dtype=torch.float64, device=f"cuda:{local}")

@@ -40,8 +40,22 @@ __global__ void __launch_bounds__(256)
 k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         const double* __restrict__ xstar, const Hyper* __restrict__ hyper, double nugget,
         double* __restrict__ mats, int mode, int full, const double* __restrict__ rows) {
-  const int ti = blockIdx.x / g.nt, tj = blockIdx.x % g.nt;
-  if (!full && ti < g.nt && tj > ti) return;  // strictly-upper tiles are never read
+  int ti, tj;
+  if (full) {
+    ti = blockIdx.x / g.nt; tj = blockIdx.x % g.nt;
+  } else {
+    // strictly-upper tiles are never read: the grid enumerates the lower trapezoid only
+    const int tri = g.nt * (g.nt + 1) / 2;
+    const int idx = blockIdx.x;
+    if (idx < tri) {
+      ti = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
+      while (ti * (ti + 1) / 2 > idx) --ti;
+      while ((ti + 1) * (ti + 2) / 2 <= idx) ++ti;
+      tj = idx - ti * (ti + 1) / 2;
+    } else {
+      ti = g.nt + (idx - tri) / g.nt; tj = (idx - tri) % g.nt;
+    }
+  }
   const int b = blockIdx.y;
   __shared__ double rx[2][TILE], cx[2][TILE], cy[TILE], cm[TILE];
   __shared__ Hyper h;
@@ -125,7 +139,8 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
 void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
                   const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
                   int full, const double* rows) {
-  dim3 grid(g.rt * g.nt, g.batch);
+  const int tiles = full ? g.rt * g.nt : g.nt * (g.nt + 1) / 2 + (g.rt - g.nt) * g.nt;
+  dim3 grid(tiles, g.batch);
   k_build<<<grid, 256, 0, st>>>(g, x, y, xstar, hyper, nugget, mats, mode, full, rows);
 }
 

@@ -332,6 +332,9 @@ __device__ __forceinline__ int wait_counter_serving(const int* ctr, int need, in
   }
 }
 
+// TRACE = true is the schedule-analysis build of the same kernel (gpb_set_trace); the production
+// instantiation carries no timestamp code or registers.
+template <bool TRACE>
 __global__ void __launch_bounds__(NTHREADS, GPB_MINBLOCKS)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapL, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
@@ -477,7 +480,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     if (tid == 0) mbar_arrive(&sm.tq_empty[slot]);
     ++q;
     if (t < 0) break;
-    unsigned long long* tr = (trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
+    unsigned long long* tr = (TRACE && trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
     if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); }
     const TaskDesc d = decode_task(g, t, jcache);
     double* M = mats + (size_t)d.b * g.mat_stride;
@@ -735,7 +738,8 @@ static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
 
 int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,
                 SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace) {
-  cudaFuncSetAttribute(k_chol_tasks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+  cudaFuncSetAttribute(k_chol_tasks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+  cudaFuncSetAttribute(k_chol_tasks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
   Geom g = g_in;
   if (mode != 0 || g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;  // debug mode: one group
   CUtensorMap tmap;
@@ -761,16 +765,20 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
     const long long slots = (long long)num_sms * ctas;
     int grid = (int)(total < slots ? total : slots);
-    k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                           (int)total, 0, solve_only, trace);
+    if (trace)
+      k_chol_tasks<true><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                   (int)total, 0, solve_only, trace);
+    else
+      k_chol_tasks<false><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                    (int)total, 0, solve_only, trace);
     launches = 1;
   } else {
     // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
     auto run = [&](long long begin, long long count) {
       if (count <= 0) return;
       int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
-      k_chol_tasks<<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
-                                                             (int)begin, (int)(begin + count), 1, solve_only, trace);
+      k_chol_tasks<false><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
+                                                                    (int)begin, (int)(begin + count), 1, solve_only, nullptr);
       ++launches;
     };
     run(0, g.batch);

@@ -414,6 +414,44 @@ def extras_single_gpu(ctx, ds, G):
         ds4.close()
         return res
 
+    def c1():
+        """configs[0]: the shipped example (SimulatedGp.scala): 1-D, n=300 sorted U(-10,10), SE+white,
+        2 chains, log-normal random walk delta=0.05; GPU device-resident MH vs the CPU oracle running
+        the reference's 2 evaluations per iteration (cpu_baseline leg: the oracle is only timed)."""
+        from oracle import oracle as o
+        r1 = np.random.default_rng(1)
+        n, chains, iters = 300, 2, 300
+        x1 = np.sort(r1.uniform(-10, 10, n)); y1 = r1.standard_normal(n) * 1.8
+        ds1 = ctx.dataset(x1, y1)
+        inits = [gterms(TRUE_TERMS)] * chains
+        z, u = G.philox_streams(11, 0, chains, iters, 3)
+        ds1.mh_run(inits, IG3, 0.05, z[:5], u[:5], on_notpd=1)
+        t0 = time.perf_counter(); ds1.mh_run(inits, IG3, 0.05, z, u, on_notpd=1); w = time.perf_counter() - t0
+        ds1.close()
+        it_cpu = 40
+        t0 = time.perf_counter()
+        o.mh_run(x1, y1, TRUE_TERMS, IG3, 0.05, z[:it_cpu, 0], u[:it_cpu, 0], evals_per_iter=2)
+        wc = time.perf_counter() - t0
+        return {"n": n, "chains": chains, "gpu_iters_per_sec_e2e": iters / w,
+                "cpu_oracle_iters_per_sec_one_chain_one_core": it_cpu / wc,
+                "note": "CPU = oracle port, 2 likelihood evaluations per iteration like Breeze metropolis; GPU = 1"}
+
+    def cpu_lapack():
+        """scipy/OpenBLAS dpotrf + dtrsv on all host cores, same n=4096 system."""
+        import scipy.linalg as sl
+        xx, yy = make_dataset()
+        d2 = ((xx[:, None, :] - xx[None, :, :]) ** 2).sum(-1)
+        K = 3.0 * np.exp(-d2 / 30.25) + 0.501 * np.eye(N_TRAIN)
+        sl.cholesky(K, lower=True)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            L = sl.cholesky(K, lower=True); sl.solve_triangular(L, yy, lower=True)
+        dt = (time.perf_counter() - t0) / 3
+        return {"factor_plus_solve_ms": dt * 1e3, "evals_per_sec_factor_only_path": 1.0 / dt, "cores": os.cpu_count(),
+                "note": "LAPACK time excludes the covariance build"}
+
+    guarded("c1_example_mcmc_n300", c1)
+    guarded("cpu_lapack_b2_n4096", cpu_lapack)
     guarded("c2_single_proposal_latency", latency)
     guarded("c2_predict_m4096", c2_predict)
     guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10))

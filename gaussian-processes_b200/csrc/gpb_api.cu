@@ -273,16 +273,18 @@ int gpb_predict(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, int 
   rc = fill_hyper(&ctx->h_hyper[0], terms, nterms, nullptr, 0, ds->dim);
   if (rc) return rc;
   const size_t nx = (size_t)m * ds->dim;
-  if ((rc = grow(ctx, &ctx->aux, &ctx->aux_doubles, nx + 2 * (size_t)m))) return rc;
+  const size_t npart = 2 * (size_t)pred_slices(g) * m;
+  if ((rc = grow(ctx, &ctx->aux, &ctx->aux_doubles, nx + 2 * (size_t)m + npart))) return rc;
   double* d_xstar = ctx->aux;
   double* d_mean = ctx->aux + nx;
   double* d_var = d_mean + m;
+  double* d_part = d_var + m;
   CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper), cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaMemcpyAsync(d_xstar, xstar, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
   rc = run_system(ctx, g, ds->x, ds->y, d_xstar, nugget);
   if (rc) return rc;
-  launch_pred_epilogue(ctx->stream, g, ctx->mats, ctx->hyper, d_mean, d_var);
-  ctx->launches += 1;
+  launch_pred_epilogue(ctx->stream, g, ctx->mats, ctx->hyper, d_part, d_mean, d_var);
+  ctx->launches += 2;
   CK(cudaMemcpyAsync(mean, d_mean, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(var, d_var, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
   int h_info = 0;

@@ -65,7 +65,7 @@ constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 struct __align__(128) CholSmem {
   double stage[STAGES][STAGE_DOUBLES];  // [0..KC) panel j ("c" rows), [KC..2KC) panel i ("r" rows)
   double Cs[TILE * LDT];                // C tile, column-major [c][r]
-  double colbuf[2][2 * TILE];
+  double colbuf[2][2][2 * TILE];        // diagonal panel: two columns per barrier, double-buffered
   uint64_t full[STAGES], empty[STAGES];
   uint64_t tq_full[2], tq_empty[2];
   uint64_t rel_full[2], rel_empty[2];   // consumer -> producer: "tile stored, publish it"
@@ -206,20 +206,37 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       for (int q = 0; q < PB; ++q) p[q] = wcol(sm, s0, c0 + q)[rr];
     }
 #pragma unroll
-    for (int q = 0; q < PB; ++q) {
-      double* cb = sm.colbuf[q & 1];
-      if (act) cb[tid] = p[q];
+    for (int q = 0; q < PB; q += 2) {
+      // two columns per barrier: every thread rebuilds column c+1 after the elimination of column c
+      // from the two published (pre-elimination) columns, so the second publish + barrier is saved
+      double* cb0 = sm.colbuf[(q >> 1) & 1][0];
+      double* cb1 = sm.colbuf[(q >> 1) & 1][1];
+      if (act) { cb0[tid] = p[q]; cb1[tid] = p[q + 1]; }
       bar_named(1, NCONS);
-      const double a = cb[c0 + q];                 // pivot (Schur complement diagonal)
-      if (tid == c0 + q && !(a > 0.0) && sm.bad_col < 0) sm.bad_col = c0 + q;  // first bad column
-      const double f = p[q] * fast_rcp(a);         // v_c(r) / a
+      const int c = c0 + q;
+      const double a0 = cb0[c];                    // pivot of column c (Schur complement diagonal)
+      const double w = cb0[c + 1];                 // entry (c+1, c)
+      if (tid == c && !(a0 > 0.0) && sm.bad_col < 0) sm.bad_col = c;   // first bad column only
+      const double r0 = fast_rcp(a0);
+      const double gm = w * r0;
+      const double a1 = fma(-gm, w, cb1[c + 1]);   // pivot of column c+1 after eliminating column c
+      if (tid == c + 1 && (a0 > 0.0) && !(a1 > 0.0) && sm.bad_col < 0) sm.bad_col = c + 1;
+      const double r1 = fast_rcp(a1);
+      const double f0 = p[q] * r0;                 // v_c(r) / a0
+      const double p1 = fma(-f0, w, p[q + 1]);     // own entry of column c+1 after column c
+      const double f1 = p1 * r1;
 #pragma unroll
-      for (int q2 = q + 1; q2 < PB; ++q2) p[q2] = fma(-f, cb[c0 + q2], p[q2]);
-      // off the chain: scaled column entry; the pivot gets one more Newton step (L_cc ~0.5 ulp)
-      const double rs = fast_rsqrt(a);
-      double l = p[q] * rs;
-      if (tid == c0 + q) { const double s0v = a * rs; l = fma(0.5 * rs, fma(-s0v, s0v, a), s0v); }
-      p[q] = l;
+      for (int q2 = q + 2; q2 < PB; ++q2) {
+        const double x0 = cb0[c0 + q2], x1 = cb1[c0 + q2];
+        const double v1 = fma(-gm, x0, x1);        // entry (c0+q2, c+1) after column c
+        p[q2] = fma(-f1, v1, fma(-f0, x0, p[q2]));
+      }
+      // off the chain: scaled column entries; the pivots get one more Newton step (L_cc ~0.5 ulp)
+      const double rs0 = fast_rsqrt(a0), rs1 = fast_rsqrt(a1);
+      double l0 = p[q] * rs0, l1 = p1 * rs1;
+      if (tid == c) { const double s0v = a0 * rs0; l0 = fma(0.5 * rs0, fma(-s0v, s0v, a0), s0v); }
+      if (tid == c + 1) { const double s1v = a1 * rs1; l1 = fma(0.5 * rs1, fma(-s1v, s1v, a1), s1v); }
+      p[q] = l0; p[q + 1] = l1;
     }
     if (top) {
 #pragma unroll
@@ -655,8 +672,9 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
         const int kend = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
+        const int kfull = kend - (CTW - 1) * 8;   // below this every column tile of the warp is live
 #pragma unroll 2
-        for (int k0 = 0; k0 < kend; k0 += 4) {
+        for (int k0 = 0; k0 < kfull; k0 += 4) {
           const int k = k0 + tq;
           double a[CTW], bb[2];
 #pragma unroll
@@ -667,6 +685,23 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           for (int ct = 0; ct < CTW; ++ct)
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) dmma884(x[ct][nt][0], x[ct][nt][1], a[ct], bb[nt]);
+        }
+        // triangular tail: column tile ct only has k < kfull + ct*8 (L^-T is lower triangular)
+#pragma unroll
+        for (int t8 = 1; t8 < CTW; ++t8) {
+#pragma unroll
+          for (int kk = 0; kk < 8; kk += 4) {
+            const int k = kfull + (t8 - 1) * 8 + kk + tq;
+            double bb[2];
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) bb[nt] = sm.Cs[k * LDT + rq * 16 + nt * 8 + gq];
+#pragma unroll
+            for (int ct = t8; ct < CTW; ++ct) {
+              const double a = LTs[(ct * 8 + gq) * LDT + k];
+#pragma unroll
+              for (int nt = 0; nt < 2; ++nt) dmma884(x[ct][nt][0], x[ct][nt][1], a, bb[nt]);
+            }
+          }
         }
 #pragma unroll
         for (int ct = 0; ct < CTW; ++ct)

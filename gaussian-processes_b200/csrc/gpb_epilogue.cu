@@ -42,21 +42,23 @@ k_ll_epilogue(Geom g, const double* __restrict__ mats, const int* __restrict__ i
   }
 }
 
-// one thread per test point j; consecutive threads read consecutive rows of a column (coalesced)
+// one thread per test point j; consecutive threads read consecutive rows of a column (coalesced).
+// The n columns are cut into gridDim.y contiguous slices (partial sums in `part`, then a fixed-order
+// second pass): enough CTAs to fill the machine at m ~ 10^4, and still bit-reproducible.
 __global__ void __launch_bounds__(128)
-k_pred_epilogue(Geom g, const double* __restrict__ mats, const Hyper* __restrict__ hyper,
-                double* __restrict__ mean, double* __restrict__ var) {
+k_pred_partial(Geom g, const double* __restrict__ mats, double* __restrict__ part, int cols_per_slice) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const double* M = mats;  // predictive is single-proposal
   __shared__ double us[128];
   double mu = 0.0, vv = 0.0;
   const size_t row = (size_t)g.npad + j;
-  for (int c0 = 0; c0 < g.n; c0 += 128) {
+  const int cbeg = blockIdx.y * cols_per_slice, cstop = min(g.n, cbeg + cols_per_slice);
+  for (int c0 = cbeg; c0 < cstop; c0 += 128) {
     __syncthreads();
-    if (c0 + threadIdx.x < g.n) us[threadIdx.x] = M[(size_t)(c0 + threadIdx.x) * g.ld + g.rhs_row];
+    if (c0 + threadIdx.x < cstop) us[threadIdx.x] = M[(size_t)(c0 + threadIdx.x) * g.ld + g.rhs_row];
     __syncthreads();
     if (j < g.m) {
-      const int cend = min(128, g.n - c0);
+      const int cend = min(128, cstop - c0);
       for (int c = 0; c < cend; ++c) {
         const double v = M[(size_t)(c0 + c) * g.ld + row];
         mu = fma(v, us[c], mu);
@@ -65,13 +67,27 @@ k_pred_epilogue(Geom g, const double* __restrict__ mats, const Hyper* __restrict
     }
   }
   if (j < g.m) {
-    // kyy = covFn(dist(xs, xs)) = covFn(0): every SE contributes h, every White its sigma
-    const Hyper& h = hyper[0];
-    double k0 = 0.0;
-    for (int t = 0; t < h.nterms; ++t) k0 = k0 + h.p0[t];
-    mean[j] = mu;
-    var[j] = k0 - vv;
+    part[((size_t)blockIdx.y * 2 + 0) * g.m + j] = mu;
+    part[((size_t)blockIdx.y * 2 + 1) * g.m + j] = vv;
   }
+}
+
+__global__ void __launch_bounds__(128)
+k_pred_finalize(Geom g, const double* __restrict__ part, int slices, const Hyper* __restrict__ hyper,
+                double* __restrict__ mean, double* __restrict__ var) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= g.m) return;
+  double mu = 0.0, vv = 0.0;
+  for (int s = 0; s < slices; ++s) {
+    mu += part[((size_t)s * 2 + 0) * g.m + j];
+    vv += part[((size_t)s * 2 + 1) * g.m + j];
+  }
+  // kyy = covFn(dist(xs, xs)) = covFn(0): every SE contributes h, every White its sigma
+  const Hyper& h = hyper[0];
+  double k0 = 0.0;
+  for (int t = 0; t < h.nterms; ++t) k0 = k0 + h.p0[t];
+  mean[j] = mu;
+  var[j] = k0 - vv;
 }
 
 // Gibbs step of the plane mean (MeanParameters.samplePlane, MeanParameters.scala:74-103): with the
@@ -178,9 +194,17 @@ void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, cons
                         gpb_ll* out) {
   k_ll_epilogue<<<g.batch, 256, 0, st>>>(g, mats, info, out);
 }
+int pred_slices(const Geom& g) {
+  int s = (g.n + 2047) / 2048;
+  return s < 1 ? 1 : (s > 32 ? 32 : s);
+}
 void launch_pred_epilogue(cudaStream_t st, const Geom& g, const double* mats, const Hyper* hyper,
-                          double* mean, double* var) {
-  k_pred_epilogue<<<(g.m + 127) / 128, 128, 0, st>>>(g, mats, hyper, mean, var);
+                          double* part, double* mean, double* var) {
+  const int slices = pred_slices(g);
+  const int cols = ((g.n + slices - 1) / slices + 127) / 128 * 128;
+  dim3 grid((g.m + 127) / 128, slices);
+  k_pred_partial<<<grid, 128, 0, st>>>(g, mats, part, cols);
+  k_pred_finalize<<<(g.m + 127) / 128, 128, 0, st>>>(g, part, slices, hyper, mean, var);
 }
 void launch_zero_upper(cudaStream_t st, const Geom& g, double* mats) {
   dim3 grid(g.n, g.batch);

@@ -41,8 +41,10 @@ void launch_plane_epilogue(cudaStream_t st, const Geom& g, const double* mats, c
 void launch_draw(cudaStream_t st, const Geom& g, const double* mats, const double* z, const double* mu,
                  double* out);
 // Predictive mean / variance per test point.
+// part: scratch of 2 * pred_slices(g) * m doubles (column-slice partial sums, reduced in fixed order).
+int pred_slices(const Geom& g);
 void launch_pred_epilogue(cudaStream_t st, const Geom& g, const double* mats, const Hyper* hyper,
-                          double* mean, double* var);
+                          double* part, double* mean, double* var);
 // Identity on the padded diagonal (matrix-level gpb_potrf input).
 void launch_pad_identity(cudaStream_t st, const Geom& g, double* mats);
 // Zero the strict upper triangle of the top square (matrix-level gpb_potrf output).

@@ -217,11 +217,15 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       const double a0 = cb0[c];                    // pivot of column c (Schur complement diagonal)
       const double w = cb0[c + 1];                 // entry (c+1, c)
       if (tid == c && !(a0 > 0.0) && sm.bad_col < 0) sm.bad_col = c;   // first bad column only
+      // 1/a1 = a0 / (a0 b1 - w^2): the two reciprocals do not depend on each other, which takes one
+      // whole reciprocal (5 dependent FP64 operations) off the per-pair dependency chain
+      const double det = fma(a0, cb1[c + 1], -(w * w));
       const double r0 = fast_rcp(a0);
+      const double rd = fast_rcp(det);
       const double gm = w * r0;
-      const double a1 = fma(-gm, w, cb1[c + 1]);   // pivot of column c+1 after eliminating column c
+      const double a1 = det * r0;                  // pivot of column c+1 after eliminating column c
       if (tid == c + 1 && (a0 > 0.0) && !(a1 > 0.0) && sm.bad_col < 0) sm.bad_col = c + 1;
-      const double r1 = fast_rcp(a1);
+      const double r1 = a0 * rd;
       const double f0 = p[q] * r0;                 // v_c(r) / a0
       const double p1 = fma(-f0, w, p[q + 1]);     // own entry of column c+1 after column c
       const double f1 = p1 * r1;

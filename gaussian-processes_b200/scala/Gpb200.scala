@@ -7,6 +7,8 @@
 //   GaussianProcess.loglikelihood  GaussianProcess.scala:109-127  -> Gpb200.loglikelihood
 //   Predict.fit                    Predict.scala:57-94            -> Gpb200.fit
 //   KernelParameters.sample        KernelParameters.scala:231-246 -> unchanged (it calls loglikelihood)
+//   MeanParameters.samplePlane     MeanParameters.scala:74-103    -> Gpb200.samplePlane
+//   GaussianProcess.draw           GaussianProcess.scala:67-83    -> Gpb200.draw
 package com.github.jonnylaw.gp
 
 import java.lang.foreign._
@@ -132,6 +134,52 @@ object Gpb200 {
       newXs.zipWithIndex.map { case (l, i) =>
         (l, Gaussian(mean.getAtIndex(JAVA_DOUBLE, i), math.sqrt(vari.getAtIndex(JAVA_DOUBLE, i))))
       }
+    } finally a.close()
+  }
+
+  private val samplePlaneH = fn("gpb_sample_plane", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+    JAVA_INT, JAVA_DOUBLE, JAVA_INT, ADDRESS, JAVA_DOUBLE, JAVA_DOUBLE, ADDRESS, ADDRESS, ADDRESS))
+  private val drawH = fn("gpb_draw", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS,
+    ADDRESS, JAVA_INT, JAVA_DOUBLE, ADDRESS, ADDRESS, ADDRESS, ADDRESS))
+
+  /** Same signature as MeanParameters.samplePlane (MeanParameters.scala:74-79).  The design matrix is
+    * built by the reference's own makeDesignMatrix (layout untouched) and handed over column-major. */
+  def samplePlane(prior: Gaussian, obs: Vector[Data], xs: Vector[Location[Double]],
+                  dist: (Location[Double], Location[Double]) => Double, p: Parameters): MeanParameters = {
+    requireEuclidean(dist)
+    val a = Arena.ofConfined()
+    try {
+      val (x, dim) = soa(xs, a)
+      val y = a.allocateFrom(JAVA_DOUBLE, obs.map(_.y): _*)
+      val dsOut = a.allocate(ADDRESS)
+      check(dsCreate.invoke(ctx.get, xs.size, dim, x, y, dsOut).asInstanceOf[Int])
+      val ds = dsOut.get(ADDRESS, 0)
+      val design = MeanParameters.makeDesignMatrix(xs)            // n x d, column-major == [d][n]
+      val d = design.cols
+      val z = a.allocateFrom(JAVA_DOUBLE, Seq.fill(d)(Gaussian(0, 1).draw): _*)
+      val beta = a.allocate(JAVA_DOUBLE, d); val info = a.allocate(JAVA_INT)
+      check(samplePlaneH.invoke(ctx.get, ds, terms(p.kernelParameters, a), p.kernelParameters.size, 1e-6, d,
+        a.allocateFrom(JAVA_DOUBLE, design.toArray: _*), prior.mean, prior.variance, z, beta, info).asInstanceOf[Int])
+      dsDestroy.invoke(ds)
+      if (info.get(JAVA_INT, 0) != 0)
+        throw new breeze.linalg.NotConvergedException(breeze.linalg.NotConvergedException.Divergence)
+      MeanParameters.plane(breeze.linalg.DenseVector(beta.toArray(JAVA_DOUBLE)))
+    } finally a.close()
+  }
+
+  /** Same signature as GaussianProcess.draw (GaussianProcess.scala:67-69); Cholesky root. */
+  def draw(xs: Vector[Location[Double]], dist: (Location[Double], Location[Double]) => Double,
+           p: Parameters): breeze.linalg.DenseVector[Double] = {
+    requireEuclidean(dist)
+    val a = Arena.ofConfined()
+    try {
+      val (x, dim) = soa(xs, a)
+      val mu = a.allocateFrom(JAVA_DOUBLE, xs.map(MeanFunction.apply(p.meanParameters)): _*)
+      val z = a.allocateFrom(JAVA_DOUBLE, Seq.fill(xs.size)(Gaussian(0, 1).draw): _*)
+      val out = a.allocate(JAVA_DOUBLE, xs.size); val info = a.allocate(JAVA_INT)
+      check(drawH.invoke(ctx.get, xs.size, dim, x, terms(p.kernelParameters, a), p.kernelParameters.size,
+        1e-3, mu, z, out, info).asInstanceOf[Int])
+      breeze.linalg.DenseVector(out.toArray(JAVA_DOUBLE))
     } finally a.close()
   }
 }

@@ -14,10 +14,11 @@ int cuda_fail(gpb_ctx* ctx, cudaError_t e, const char* where) {
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // m test points + (with_rhs ? 1 : 0) rhs row appended below the npad x npad square
-Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design) {
+Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design, bool identity) {
   Geom g;
-  g.n = n; g.dim = dim; g.m = m; g.design = design;
   g.npad = round_up(n, TILE);
+  if (identity) { m = 0; design = g.npad; }
+  g.n = n; g.dim = dim; g.m = m; g.design = design;
   g.apad = round_up(m + design + (with_rhs ? 1 : 0), TILE);
   g.ld = g.npad + g.apad;
   g.nt = g.npad / TILE;
@@ -25,6 +26,7 @@ Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design) {
   g.rhs_row = with_rhs ? g.npad + m + design : -1;
   g.batch = batch;
   g.tgroup = batch;
+  g.ident0 = identity ? g.nt : -1;
   g.mat_stride = (size_t)g.ld * g.npad;
   return g;
 }

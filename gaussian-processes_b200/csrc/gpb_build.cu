@@ -126,7 +126,8 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);  // GaussianProcess.scala:117-118
       }
     } else if (rclass == 5) {
-      v = rows[(size_t)(R - g.npad - g.m) * g.n + Cc];  // design-matrix column (MeanParameters.scala:55-65)
+      // design-matrix column (MeanParameters.scala:55-65), or a row of the identity block
+      v = (g.ident0 >= 0) ? ((R - g.npad == Cc) ? 1.0 : 0.0) : rows[(size_t)(R - g.npad - g.m) * g.n + Cc];
     } else if (rclass == 3) {
       v = cy[cl] - cm[cl];  // GaussianProcess.scala:120-122
     } else {

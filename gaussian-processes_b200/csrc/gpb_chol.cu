@@ -134,6 +134,20 @@ __device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcach
   return d;
 }
 
+// First block column of the contraction of task (i, j): 0 in general.  Tile row I = i - ident0 of an
+// appended identity block is zero left of block column I, so its contraction starts at I and the
+// tasks left of it are void (k_build wrote the zeros, launch_chol presets done[i] = I).  -1 = void.
+__device__ __forceinline__ int task_k0(const Geom& g, const TaskDesc& d) {
+  if (g.ident0 < 0 || d.i < g.ident0) return 0;
+  const int I = d.i - g.ident0;
+  if (I >= g.nt) return 0;   // the rhs rows behind the identity block are dense
+  return d.j < I ? -1 : I;
+}
+__global__ void k_preset_ident_done(Geom g, int* __restrict__ done) {
+  const int I = blockIdx.x * blockDim.x + threadIdx.x;
+  if (I < g.nt) done[(size_t)blockIdx.y * g.rt + g.ident0 + I] = I;
+}
+
 __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* error) {
   if (ld_acquire(ctr) >= need) return true;
   long long t0 = clock64();
@@ -401,12 +415,13 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       }
       ++q;
       if (t < 0) break;
-      if (!solve_only) ++posted;
       const TaskDesc d = decode_task(g, t, jcache);
-      if (solve_only && d.i < g.nt) {          // L is given: no accumulation for top-square tiles
+      const int k0 = task_k0(g, d);
+      if ((solve_only && d.i < g.nt) || k0 < 0) {   // L is given: no accumulation for top-square tiles; void task
         if (lane == 0) t_next = fetch();
         continue;
       }
+      if (!solve_only) ++posted;
       const int* done_b = done + (size_t)d.b * g.rt;
       if (lane == 0) {
         // the tile itself (accumulator start value) comes first, as AT_STAGES ordinary stages:
@@ -424,7 +439,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
         // progress counters only grow: poll again only when the last value seen is not enough
         int seen_i = 0, seen_j = 0;
-        for (int kc = 0; kc < d.j; ++kc) {
+        for (int kc = k0; kc < d.j; ++kc) {
           bool polled = false;
           if (seen_i < kc + 1) { seen_i = wait_counter_serving(done_b + d.i, kc + 1, &sched->error, sm, rs); polled = true; }
           if (seen_j < kc + 1) { seen_j = wait_counter_serving(done_b + d.j, kc + 1, &sched->error, sm, rs); polled = true; }
@@ -504,6 +519,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     unsigned long long* tr = (TRACE && trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
     if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); }
     const TaskDesc d = decode_task(g, t, jcache);
+    const int k0 = task_k0(g, d);
+    if (k0 < 0) continue;
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
     double* Aij = M + (size_t)(d.j * TILE) * g.ld + (size_t)d.i * TILE;  // (r, c) at Aij[c*ld + r]
@@ -559,7 +576,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       }
     };
 
-    const int nstage = (solve_only && d.i < g.nt) ? 0 : d.j * (TILE / KC);
+    const int nstage = (solve_only && d.i < g.nt) ? 0 : (d.j - k0) * (TILE / KC);
     // Stage release is DELAYED by one stage: ptxas schedules mbarrier.arrive right behind the last
     // LDS of a stage without waiting for those loads to return, and with two CTAs per SM the
     // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
@@ -763,7 +780,7 @@ static bool make_tmap_linvt(CUtensorMap* tm, const Geom& g, double* linvt) {
                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-static bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
+bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
   EncodeFn encode = tmap_encoder();
   if (!encode) return false;
   const cuuint64_t dims[3] = {(cuuint64_t)g.ld, (cuuint64_t)g.npad, (cuuint64_t)g.batch};
@@ -788,8 +805,12 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
   cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
   cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
-  cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   int launches = 0;
+  if (g.ident0 >= 0) {
+    k_preset_ident_done<<<dim3((g.nt + 127) / 128, g.batch), 128, 0, st>>>(g, done);
+    ++launches;
+  }
+  cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   if (mode == 0) {
     // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; single small proposals
     // are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA that
@@ -810,7 +831,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     else
       k_chol_tasks<false><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
                                                                     (int)total, 0, solve_only, trace);
-    launches = 1;
+    ++launches;
   } else {
     // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
     auto run = [&](long long begin, long long count) {

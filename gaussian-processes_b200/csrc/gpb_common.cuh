@@ -26,6 +26,7 @@ struct Hyper {
 // Geometry of one (batched) tall lower-trapezoidal system:
 //   rows  0 .. npad-1           training points (identity-padded to a multiple of TILE)
 //   rows  npad .. npad+apad-1   appended rows: m test points (K* rows), `design` explicit rows, then one rhs row (y - m(x))
+//                               (identity mode: m == 0 and the `design` = npad rows are I, solved to L^-T)
 // stored column-major, leading dimension ld = npad + apad, npad columns, one matrix per proposal.
 struct Geom {
   int n, dim, m;        // training size, input dimension, number of test points
@@ -35,6 +36,7 @@ struct Geom {
   int rhs_row;          // absolute row index of the rhs row (npad + m)
   int batch;
   int tgroup;           // proposals per ticket group of the factorisation kernel (<= batch)
+  int ident0;           // first tile row of an appended identity block (npad rows -> L^-T), or -1
   size_t mat_stride;    // doubles between consecutive matrices
 };
 

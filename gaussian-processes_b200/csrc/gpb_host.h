@@ -76,7 +76,7 @@ int grow_pinned(gpb_ctx* ctx, T** p, size_t* have, size_t want) {
   return GPB_OK;
 }
 
-Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design = 0);
+Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design = 0, bool identity = false);
 int ensure_workspace(gpb_ctx* ctx, const Geom& g);
 int fill_hyper(Hyper* h, const gpb_term* terms, int nterms, const double* beta, int nbeta, int dim);
 int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y,

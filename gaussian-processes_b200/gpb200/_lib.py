@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("GPB200_LIB") or os.path.join(_PKG, "libgpb200.so")
 
 KIND_SE, KIND_WHITE, KIND_MATERN = 0, 1, 2
 FORMULA_AS_PARSED, FORMULA_GPML = 0, 1
+GRAD_AS_EXECUTED, GRAD_ANALYTIC = 0, 1
 
 EXPORTS = [
     "gpb_ctx_create", "gpb_ctx_destroy", "gpb_dataset_create", "gpb_dataset_destroy",
@@ -21,7 +22,7 @@ EXPORTS = [
     "gpb_build_cov", "gpb_potrf", "gpb_trsm_lower", "gpb_trsm_upper", "gpb_mh_run",
     "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
     "gpb_last_timing", "gpb_set_sched", "gpb_set_trace", "gpb_get_trace", "gpb_version",
-    "gpb_plane_stats", "gpb_sample_plane", "gpb_draw",
+    "gpb_plane_stats", "gpb_sample_plane", "gpb_draw", "gpb_mll_gradient",
 ]
 
 
@@ -95,6 +96,8 @@ def load():
                                    _dp, C.c_double, C.c_double, _dp, _dp, _ip]
     L.gpb_draw.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, C.POINTER(Term), C.c_int, C.c_double,
                            _dp, _dp, _dp, _ip]
+    L.gpb_mll_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(Term), C.c_int, _dp, C.c_int,
+                                   C.c_double, C.c_int, _dp, _ip]
     L.gpb_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     L.gpb_set_sched.argtypes = [C.c_void_p, C.c_int]
     L.gpb_set_trace.argtypes = [C.c_void_p, C.c_int]
@@ -288,6 +291,26 @@ class Dataset:
         ctx._check(ctx.L.gpb_loglik_batch(ctx.h, self.h, batch, arr, nterms, bptr, nbeta,
                                           float(nugget), out))
         return out
+
+    def mll_gradient(self, term_lists, betas=None, nugget=1e-3, mode=GRAD_AS_EXECUTED):
+        """term_lists: [batch][nterms] of (kind, p0, p1) holding the UNCONSTRAINED (log) parameters.
+        Returns (grad [batch][P], info [batch])."""
+        ctx = self.ctx
+        arr, nterms = terms_array(term_lists)
+        batch = len(term_lists)
+        if betas is None or len(betas) == 0 or len(betas[0]) == 0:
+            bptr, nbeta = None, 0
+        else:
+            bv = as_f64(betas)
+            if bv.shape[0] != batch:
+                raise ValueError("one beta vector per proposal")
+            bptr, nbeta = _ptr(bv), bv.shape[1]
+        P = sum(2 if t[0] == 0 else 1 for t in term_lists[0])
+        grad = np.empty((batch, P))
+        info = np.zeros(batch, dtype=np.int32)
+        ctx._check(ctx.L.gpb_mll_gradient(ctx.h, self.h, batch, arr, nterms, bptr, nbeta, float(nugget),
+                                          int(mode), _ptr(grad), info.ctypes.data_as(_ip)))
+        return grad, info
 
     def predict(self, terms, xstar, nugget=1e-6):
         ctx = self.ctx

@@ -163,6 +163,26 @@ int gpb_sample_plane(gpb_ctx *ctx, const gpb_dataset *ds, const gpb_term *terms,
 int gpb_draw(gpb_ctx *ctx, int n, int dim, const double *x, const gpb_term *terms, int nterms,
              double nugget, const double *mu, const double *z, double *out, int *info);
 
+/* GaussianProcess.mllGradient(observed, dist)(p)  GaussianProcess.scala:166-187, with the tangent
+ * matrices of KernelParameters.tangentMatrix / gradient (KernelParameters.scala:270-300): the input
+ * of the HMC samplers (KernelParameters.scala:121-198).  `terms` hold the parameters as the reference
+ * passes them to mllGradient, i.e. UNCONSTRAINED (log scale; sampleHmc :141-144).  grad: [batch][P] in
+ * Parameters.toList order of the kernel terms; info: [batch].  K^-1 is never materialised: L^-T rides
+ * the factorisation as an appended identity block, and a fused DMMA contraction + epilogue forms
+ * 0.5 sum_ij (alpha_i alpha_j - Kinv_ij) G_p(d_ij).
+ *   GPB_GRAD_AS_EXECUTED  what the Scala executes: kxx is built from the unconstrained values
+ *       themselves (:171-176), the tangent entries are exp(-d^2/s^2) + 1, -(2h/s^3) exp(-d^2/s^2) + 1
+ *       and 2 (white), with h, s the exponentials (:272-281).  The reference solves with LU; this
+ *       path needs kxx positive definite and reports info > 0 otherwise (grad = NaN).
+ *   GPB_GRAD_ANALYTIC     the gradient of the GPML log marginal likelihood with respect to the log
+ *       parameters: kxx from the exponentials, dK/dlog h = h E, dK/dlog s = h E 2 d^2/s^2,
+ *       dK/dlog s_w = s_w [d == 0].
+ * nugget is 1e-3 in the reference (:175). */
+#define GPB_GRAD_AS_EXECUTED 0
+#define GPB_GRAD_ANALYTIC 1
+int gpb_mll_gradient(gpb_ctx *ctx, const gpb_dataset *ds, int batch, const gpb_term *terms, int nterms,
+                     const double *beta, int nbeta, double nugget, int mode, double *grad, int *info);
+
 /* ---- misc -------------------------------------------------------------------------------- */
 const char *gpb_strerror(int status);
 const char *gpb_last_cuda_error(const gpb_ctx *ctx);

@@ -5,6 +5,7 @@ __graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference legs, 
 product package.  Parity unpinned (the reference ships no golden vectors for this path).
 """
 import ctypes as C
+import math
 import os
 import subprocess
 
@@ -238,3 +239,50 @@ def draw(x, terms, z, beta=(), nugget=1e-3):
     w, V = np.linalg.eigh(K)
     zz = np.asarray(z, dtype=np.float64)
     return mu + V @ (np.sqrt(w) * zz), mu + potrf_lower(K)[0] @ zz
+
+
+def distance_matrix(x):
+    xx = np.asarray(x, dtype=np.float64)
+    if xx.ndim == 1:
+        xx = xx[:, None]
+    d2 = (xx[:, None, 0] - xx[None, :, 0]) ** 2
+    if xx.shape[1] == 2:
+        d2 = d2 + (xx[:, None, 1] - xx[None, :, 1]) ** 2
+    return np.sqrt(d2)
+
+
+def mll_gradient(x, y, theta, beta=(), nugget=1e-3, mode="as_executed"):
+    """GaussianProcess.mllGradient (GaussianProcess.scala:166-187) with KernelParameters.tangentMatrix /
+    gradient (KernelParameters.scala:270-300), line by line.  theta: terms holding the parameters as
+    sampleHmc passes them (unconstrained / log scale).
+      as_executed: kxx = buildCov(theta AS IS) + nugget (:171-176); tangent entries exp(-d^2/s^2) + 1,
+                   -(2h/s^3) exp(-d^2/s^2) + 1 and 2 (white), h = exp(hu), s = exp(su) (:272-281);
+                   alpha = kxx \\ ys (LU); grad = 0.5 sum(diag(alpha alpha^T g - kxx \\ g)).
+      analytic:    the gradient of ll_gpml with respect to the log parameters (kxx from exp(theta))."""
+    D = distance_matrix(x)
+    n = D.shape[0]
+    xx = np.asarray(x, dtype=np.float64).reshape(n, -1)
+    ys = np.asarray(y, dtype=np.float64).copy()
+    if len(beta):
+        ys = ys - (beta[0] + xx @ np.asarray(beta[1:], dtype=np.float64))
+    if mode == "as_executed":
+        kterms = list(theta)
+    else:
+        kterms = [(t[0], math.exp(t[1]), math.exp(t[2])) if t[0] == "se" else (t[0], math.exp(t[1])) for t in theta]
+    K = build_cov(x, kterms, nugget)
+    tangents = []
+    for t in theta:
+        if t[0] == "se":
+            h, s = math.exp(t[1]), math.exp(t[2])
+            E = np.exp(-(D * D) / (s * s))
+            if mode == "as_executed":
+                tangents += [E + 1.0, -(2 * h / (s * s * s)) * E + 1.0]
+            else:
+                tangents += [h * E, h * E * 2.0 * (D * D) / (s * s)]
+        else:
+            if mode == "as_executed":
+                tangents.append(np.full((n, n), 2.0))
+            else:
+                tangents.append(math.exp(t[1]) * (D == 0.0))
+    alpha = np.linalg.solve(K, ys)
+    return np.array([0.5 * np.sum(np.diag(np.outer(alpha, alpha) @ g - np.linalg.solve(K, g))) for g in tangents])

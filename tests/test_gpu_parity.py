@@ -421,3 +421,72 @@ def test_draw_uses_the_cholesky_root(ctx, oracle):
     out, info = ctx.draw(x, gterms(SE_W), z, mu, nugget=1e-3)
     _, chol_draw = oracle.draw(x, SE_W, z, beta=(0.5, 0.1), nugget=1e-3)
     assert info == 0 and np.allclose(out, chol_draw, rtol=1e-9, atol=1e-11)
+
+
+def _theta(terms):
+    return [(t[0], math.log(t[1]), math.log(t[2])) if t[0] == "se" else (t[0], math.log(t[1])) for t in terms]
+
+
+@pytest.mark.parametrize("n,dim,terms", [(40, 1, SE_W), (130, 2, SE_W), (300, 2, SE_SE_W), (1000, 1, SE_SE_W)])
+def test_mll_gradient_parity(ctx, oracle, n, dim, terms):
+    """GaussianProcess.mllGradient through the C ABI vs the numpy restatement, both the
+    as-executed Scala formulas and the analytic gradient; plane mean; duplicate location."""
+    x, y, _ = synth(oracle, n, dim, terms, 700 + n)
+    beta = (0.2, -0.05) if dim == 1 else (0.2, -0.05, 0.03)
+    ds = ctx.dataset(x, y)
+    from gpb200 import _lib as G
+    # analytic: log parameters
+    th = _theta(terms)
+    go = oracle.mll_gradient(x, y, th, beta=beta, mode="analytic")
+    g, info = ds.mll_gradient([gterms(th)], [beta], mode=G.GRAD_ANALYTIC)
+    assert info[0] == 0
+    assert np.allclose(g[0], go, rtol=1e-8, atol=1e-8 * np.abs(go).max()), (g[0], go)
+    # as executed: kxx is built from the unconstrained values themselves -> keep them positive (kxx PD)
+    th2 = [("se", 1.1, 0.9), ("se", 0.4, 0.2), ("white", 0.3)][: len(terms) - 1] + [("white", 0.3)]
+    go2 = oracle.mll_gradient(x, y, th2, mode="as_executed")
+    g2, info2 = ds.mll_gradient([gterms(th2)], mode=G.GRAD_AS_EXECUTED)
+    assert info2[0] == 0
+    assert np.allclose(g2[0], go2, rtol=1e-8, atol=1e-8 * np.abs(go2).max()), (g2[0], go2)
+    ds.close()
+
+
+def test_mll_gradient_batch_and_not_pd(ctx, oracle):
+    x, y, _ = synth(oracle, 200, 1, SE_W, 812)
+    ds = ctx.dataset(x, y)
+    from gpb200 import _lib as G
+    ths = [[("se", math.log(3.0 + b), math.log(5.5 - b)), ("white", math.log(0.5 + 0.1 * b))] for b in range(3)]
+    g, info = ds.mll_gradient([gterms(t) for t in ths], mode=G.GRAD_ANALYTIC)
+    assert np.all(info == 0)
+    for b in range(3):
+        go = oracle.mll_gradient(x, y, ths[b], mode="analytic")
+        assert np.allclose(g[b], go, rtol=1e-8, atol=1e-8 * np.abs(go).max())
+    # as executed with a negative unconstrained white parameter: kxx is indefinite, the reference's LU
+    # would carry on; this path reports it (include/gpb200.h)
+    g, info = ds.mll_gradient([gterms([("se", 1.1, 1.7), ("white", -0.7)])], mode=G.GRAD_AS_EXECUTED)
+    assert info[0] > 0 and np.all(np.isnan(g[0]))
+    ds.close()
+
+
+def test_full_size_mll_gradient_n4096_matches_differences_of_the_device_ll(ctx, oracle):
+    """Size-independent property at C2's size: the analytic gradient is the derivative of the (parity-
+    checked) device log-likelihood; central differences in the log parameters."""
+    from gpb200 import _lib as G
+    rng = np.random.default_rng(4096)
+    n = 4096
+    x = np.sort(rng.uniform(0, 400, n))
+    y = np.sin(x / 7.0) * 2.0 + 0.7 * rng.standard_normal(n)
+    ds = ctx.dataset(x, y)
+    v0 = np.array([math.log(3.0), math.log(5.5), math.log(0.5)])
+    g, info = ds.mll_gradient([[(0, v0[0], v0[1]), (1, v0[2], 0.0)]], mode=G.GRAD_ANALYTIC)
+    assert info[0] == 0
+
+    def ll(v):
+        r = ds.loglik_batch([[(0, math.exp(v[0]), math.exp(v[1])), (1, math.exp(v[2]), 0.0)]])[0]
+        assert r.info == 0
+        return G.ll_value(r, G.FORMULA_GPML)
+
+    for p in range(3):
+        e = np.zeros(3); e[p] = 1e-4
+        fd = (ll(v0 + e) - ll(v0 - e)) / 2e-4
+        assert abs(fd - g[0][p]) < 2e-5 * max(1.0, abs(g[0][p])), (p, fd, g[0][p])
+    ds.close()

@@ -194,3 +194,32 @@ def test_sample_plane_and_draw_restatements(oracle):
     R = V * np.sqrt(w)
     assert np.allclose(R @ R.T, Lc @ Lc.T, rtol=1e-9, atol=1e-10)   # two roots of the same covariance
     assert np.allclose(eig_draw, mu + R @ ze, rtol=1e-8, atol=1e-10)
+
+
+def test_mll_gradient_restatement(oracle):
+    """SURVEY.md 8f-2.  The analytic mode is the gradient of ll_gpml in the log parameters (checked by
+    central differences); the as-executed mode follows the Scala formulas, which are NOT that gradient."""
+    rng = np.random.default_rng(77)
+    n = 60
+    x = rng.uniform(-5, 5, size=(n, 2))
+    terms = [("se", 3.0, 2.5), ("se", 0.7, 0.6), ("white", 0.5)]
+    y = np.linalg.cholesky(oracle.build_cov(x, terms, 1e-3)) @ rng.standard_normal(n) + 0.3 + 0.1 * x[:, 0]
+    beta = (0.3, 0.1, 0.0)
+    theta = [("se", math.log(3.0), math.log(2.5)), ("se", math.log(0.7), math.log(0.6)), ("white", math.log(0.5))]
+    g = oracle.mll_gradient(x, y, theta, beta=beta, mode="analytic")
+    flat = [math.log(3.0), math.log(2.5), math.log(0.7), math.log(0.6), math.log(0.5)]
+
+    def ll(v):
+        t = [("se", math.exp(v[0]), math.exp(v[1])), ("se", math.exp(v[2]), math.exp(v[3])), ("white", math.exp(v[4]))]
+        return oracle.loglik(x, y, t, beta=beta)["ll_gpml"]
+
+    for p in range(5):
+        e = np.zeros(5); e[p] = 1e-5
+        fd = (ll(np.array(flat) + e) - ll(np.array(flat) - e)) / 2e-5
+        assert abs(fd - g[p]) < 1e-5 * max(1.0, abs(g[p])), (p, fd, g[p])
+    # as executed: every tangent carries the "+ derivative" constant, the white one is the constant 2
+    ge = oracle.mll_gradient(x, y, [("se", 1.1, 0.9), ("white", 0.4)], mode="as_executed")
+    K = oracle.build_cov(x, [("se", 1.1, 0.9), ("white", 0.4)], 1e-3)
+    a = np.linalg.solve(K, y)
+    s1 = a.sum() ** 2 - np.linalg.solve(K, np.ones((n, n))).trace()
+    assert ge.shape == (3,) and abs(ge[2] - s1) < 1e-9 * abs(s1)

@@ -416,6 +416,34 @@ class GaussianProcess:
         ll.batch = lambda ps, formula=None: GaussianProcess._ll_batch(ds, ps, formula)
         return ll
 
+    gradient_mode = G.GRAD_AS_EXECUTED  # what GaussianProcess.scala:166-187 executes; G.GRAD_ANALYTIC = the true gradient
+
+    @staticmethod
+    def mllGradient(observed, dist):
+        """GaussianProcess.scala:166-187 -> gpb_mll_gradient.  Curried like the reference; p holds the
+        UNCONSTRAINED kernel parameters (that is what sampleHmc passes, KernelParameters.scala:141-144).
+        Returns the gradient per kernel parameter in toList order."""
+        _require_euclidean(dist)
+        x = _pack_locations([d.x for d in observed])
+        y = np.array([d.y for d in observed], dtype=np.float64)
+        ds = default_context().dataset(x, y)
+
+        def batch(ps, mode=None):
+            mode = GaussianProcess.gradient_mode if mode is None else mode
+            betas = [list(p.meanParameters.toList()) for p in ps]
+            g, info = ds.mll_gradient([_terms(p.kernelParameters) for p in ps], betas, nugget=1e-3, mode=mode)
+            for i in info:
+                if i != 0:
+                    raise NotConvergedException(int(i))  # the reference's LU would carry on (include/gpb200.h)
+            return g
+
+        def grad(p: Parameters, mode=None):
+            return batch([p], mode)[0]
+
+        grad.dataset = ds
+        grad.batch = batch
+        return grad
+
     @staticmethod
     def _ll_batch(ds, ps, formula=None):
         formula = GaussianProcess.formula if formula is None else formula
@@ -460,6 +488,44 @@ class KernelParameters:
                           KernelParameters.vectorToParams(p.kernelParameters, vals[n:]))
 
     @staticmethod
+    def unconstrainParams(ps):  # KernelParameters.scala:251-255
+        return [p.map(math.log) for p in ps]
+
+    @staticmethod
+    def constrainParams(ps):  # KernelParameters.scala:260-264
+        return [p.map(math.exp) for p in ps]
+
+    @staticmethod
+    def sampleHmc(ys, dist, init: Parameters, prior, m, l, eps, rng=None):
+        """KernelParameters.scala:121-156: HMC over the unconstrained parameters.  ll = prior + device
+        log-likelihood of the constrained parameters; grad = device mllGradient + prior gradient (zipped
+        like the reference).  Generator of theta arrays (MarkovChain(theta))."""
+        rng = np.random.default_rng() if rng is None else rng
+        llf = GaussianProcess.loglikelihood(ys, dist)
+        gradf = GaussianProcess.mllGradient(ys, dist)
+
+        def ll(p):
+            params = KernelParameters.arrayToParams(init, p)
+            kp = KernelParameters.constrainParams(params.kernelParameters)
+            return sum(pr.logPdf(pa) for pr, pa in zip(prior, p)) + llf(params.copy(kernelParameters=kp))
+
+        def grad(p):
+            params = KernelParameters.arrayToParams(init, p)
+            evalPrior = [pr.gradLogPdf(pa) for pr, pa in zip(prior, p)]
+            return np.array([a + b for a, b in zip(gradf(params), evalPrior)])
+
+        kp = KernelParameters.unconstrainParams(init.kernelParameters)
+        theta = KernelParameters.paramsToArray(init.copy(kernelParameters=kp))
+
+        def chain():
+            t = theta
+            while True:
+                yield t
+                t, _ = Hmc.step(eps, l, m, ll, grad)(t, rng)
+
+        return chain()
+
+    @staticmethod
     def sample(obs, dist, prior: Callable, prop: Callable):
         """KernelParameters.scala:231-246 + Breeze metropolis: returns step(p, rng) -> p'.
         prior / prop stay host closures (prop(kernelParameters, rng) -> kernelParameters).
@@ -477,6 +543,80 @@ class KernelParameters:
             return nxt if u < a else p
 
         return step
+
+
+# --------------------------------------------------------------------------------------------
+# Hmc.scala / GradDist.scala: host control flow around the device log-likelihood and gradient
+# --------------------------------------------------------------------------------------------
+
+
+class GradDist:
+    """GradDist.scala:5-24: a univariate prior with logPdf and gradLogPdf (breeze Gamma(shape, scale) /
+    Gaussian(mu, sigma)); the normal's gradient divides by sigma, as the reference does (:22)."""
+
+    def __init__(self, logPdf, gradLogPdf):
+        self.logPdf, self.gradLogPdf = logPdf, gradLogPdf
+
+    @staticmethod
+    def gamma(shape, scale):
+        return GradDist(lambda x: (shape - 1.0) * math.log(x) - x / scale - (math.lgamma(shape) + shape * math.log(scale)),
+                        lambda x: (shape - 1.0) / x - 1.0 / scale)
+
+    @staticmethod
+    def normal(mu, sigma):
+        return GradDist(lambda x: -(x - mu) ** 2 / (2.0 * sigma * sigma) - math.log(sigma * math.sqrt(2.0 * math.pi)),
+                        lambda x: -(x - mu) / sigma)
+
+
+class Hmc:
+    @staticmethod
+    def priorPhi(m, rng):  # Hmc.scala:8-11: MultivariateGaussian(0, m) = chol(m) z
+        m = np.asarray(m, dtype=np.float64)
+        return np.linalg.cholesky(m) @ rng.standard_normal(m.shape[1])
+
+    @staticmethod
+    def phiHalfStep(eps, theta, phi, gradient):  # :13-17
+        return phi + np.asarray(gradient(theta)) * 0.5 * eps
+
+    @staticmethod
+    def thetaStep(eps, theta, phi):  # :19-20
+        return theta + eps * phi
+
+    @staticmethod
+    def leapfrog(eps, gradient, theta, phi):  # :30-39
+        p1 = Hmc.phiHalfStep(eps, theta, phi, gradient)
+        t1 = Hmc.thetaStep(eps, theta, p1)
+        return t1, Hmc.phiHalfStep(eps, t1, p1, gradient)
+
+    @staticmethod
+    def leapfrogs(eps, gradient, l, theta, phi):  # :44-56
+        for _ in range(l):
+            theta, phi = Hmc.leapfrog(eps, gradient, theta, phi)
+        return theta, phi
+
+    @staticmethod
+    def kinetic(phi):  # :59-68
+        return 0.5 * float(np.sum(np.asarray(phi) ** 2))
+
+    @staticmethod
+    def logDensity(theta, phi, pos):  # :70-73
+        return pos(theta) - Hmc.kinetic(phi)
+
+    @staticmethod
+    def logAcceptance(propTheta, propPhi, theta, phi, pos):  # :78-85
+        a = Hmc.logDensity(propTheta, propPhi, pos) - Hmc.logDensity(theta, phi, pos)
+        return -math.inf if math.isnan(a) else min(a, 0.0)
+
+    @staticmethod
+    def step(eps, l, m, pos, gradient):  # :87-105
+        def run(theta, rng):
+            theta = np.asarray(theta, dtype=np.float64)
+            phi = Hmc.priorPhi(m, rng)
+            t, p = Hmc.leapfrogs(eps, gradient, l, theta, phi)
+            a = Hmc.logAcceptance(t, p, theta, phi, pos)
+            u = rng.uniform()
+            return (t, a) if math.log(u) < a else (theta, a)
+        return run
 
 
 # --------------------------------------------------------------------------------------------

@@ -232,6 +232,33 @@ struct GaussianProcess {
     return LogLikelihood(std::make_shared<detail::Dataset>(xs, y));
   }
 
+  // mllGradient(observed, dist)(p) (GaussianProcess.scala:166-187): p holds the UNCONSTRAINED kernel
+  // parameters, as sampleHmc passes them (KernelParameters.scala:141-144); one entry per kernel
+  // parameter in toList order.  gradientMode(): as executed by the Scala (default) or analytic.
+  static int& gradientMode() { static int m = GPB_GRAD_AS_EXECUTED; return m; }
+  class MllGradient {
+    std::shared_ptr<detail::Dataset> ds_;
+   public:
+    explicit MllGradient(std::shared_ptr<detail::Dataset> ds) : ds_(std::move(ds)) {}
+    std::vector<double> operator()(const Parameters& p) const {
+      const size_t nbeta = p.meanParameters.beta.size();
+      if (nbeta != 0 && (int)nbeta != ds_->dim + 1) throw std::runtime_error("Dimension mismatch");
+      auto t = detail::terms(p.kernelParameters);
+      size_t P = 0; for (const auto& k : p.kernelParameters) P += k.toList().size();
+      std::vector<double> g(P); int info = 0;
+      detail::check(gpb_mll_gradient(detail::context(), ds_->h, 1, t.data(), (int)t.size(), nbeta ? p.meanParameters.beta.data() : nullptr,
+                                     (int)nbeta, 1e-3, gradientMode(), g.data(), &info), detail::context());
+      if (info != 0) throw NotConvergedException(info);   // the reference's LU would carry on (gpb200.h)
+      return g;
+    }
+  };
+  static MllGradient mllGradient(const std::vector<Data>& observed, DistFn dist) {
+    detail::requireEuclidean(dist);
+    std::vector<Location> xs; std::vector<double> y;
+    for (const auto& d : observed) { xs.push_back(d.x); y.push_back(d.y); }
+    return MllGradient(std::make_shared<detail::Dataset>(xs, y));
+  }
+
   // GaussianProcess.scala:67-83: mu + root z, nugget 1e-3; z = the |xs| standard normals the
   // reference draws from breeze (passed in so the stream is explicit).  Cholesky root (8f-3).
   static std::vector<Data> draw(const std::vector<Location>& xs, DistFn dist, const Parameters& p, const std::vector<double>& z) {

@@ -105,6 +105,13 @@ int main() {
     vec("zb", zb);
     Parameters p{MeanParameters::plane({0.5, 0.1, -0.2}), ks};
     vec("plane_beta", MeanSampler::samplePlane(Gaussian{1.0, 2.0}, Predict::buildData(xs, y), xs, &Location::euclidean, p, zb).beta);
+    // mllGradient: unconstrained parameters; as executed (positive values keep kxx PD) and analytic
+    auto grad = GaussianProcess::mllGradient(Predict::buildData(xs, y), &Location::euclidean);
+    vec("grad_as_executed", grad(Parameters{MeanParameters::zero(), {KernelParameters::se(1.1, 0.9), KernelParameters::white(0.3)}}));
+    GaussianProcess::gradientMode() = GPB_GRAD_ANALYTIC;
+    vec("grad_analytic", grad(Parameters{MeanParameters::plane({0.5, 0.1, -0.2}),
+                                         {KernelParameters::se(std::log(3.0), std::log(5.5)), KernelParameters::white(std::log(0.5))}}));
+    GaussianProcess::gradientMode() = GPB_GRAD_AS_EXECUTED;
     std::vector<double> dr; for (auto& d : GaussianProcess::draw(xs, &Location::euclidean, p, z)) dr.push_back(d.y);
     vec("draw", dr);
   }

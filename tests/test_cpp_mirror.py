@@ -124,6 +124,17 @@ def test_sample_plane_and_draw(out, oracle):
 
 
 @pytest.mark.gpu
+def test_mll_gradient(out, oracle):
+    x = np.stack([out["xa"], out["xb"]], axis=1)
+    y = np.array(out["y2"])
+    go = oracle.mll_gradient(x, y, [("se", 1.1, 0.9), ("white", 0.3)], mode="as_executed")
+    assert np.allclose(out["grad_as_executed"], go, rtol=1e-8, atol=1e-8 * np.abs(go).max())
+    th = [("se", math.log(3.0), math.log(5.5)), ("white", math.log(0.5))]
+    ga = oracle.mll_gradient(x, y, th, beta=(0.5, 0.1, -0.2), mode="analytic")
+    assert np.allclose(out["grad_analytic"], ga, rtol=1e-8, atol=1e-8 * np.abs(ga).max())
+
+
+@pytest.mark.gpu
 def test_error_behaviour(out):
     assert out["err_mixed_dims"] == "Dimension mismatch"       # Location.scala:32
     assert out["err_not_pd"] == "NotConvergedException"        # breeze cholesky

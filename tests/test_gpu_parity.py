@@ -490,3 +490,42 @@ def test_full_size_mll_gradient_n4096_matches_differences_of_the_device_ll(ctx, 
         fd = (ll(v0 + e) - ll(v0 - e)) / 2e-4
         assert abs(fd - g[0][p]) < 2e-5 * max(1.0, abs(g[0][p])), (p, fd, g[0][p])
     ds.close()
+
+
+def test_hmc_chain_follows_the_oracle_driven_chain(oracle):
+    """KernelParameters.sampleHmc (KernelParameters.scala:121-156, Hmc.scala): the same host leapfrog
+    driven once by the device log-likelihood + gradient and once by the oracle's, same streams."""
+    import gpb200 as gp
+    rng = np.random.default_rng(31)
+    n = 120
+    xs = np.sort(rng.uniform(-10, 10, n))
+    ys = np.linalg.cholesky(oracle.build_cov(xs, SE_W, 1e-3)) @ rng.standard_normal(n)
+    observed = [gp.GaussianProcess.Data(gp.One(float(a)), float(b)) for a, b in zip(xs, ys)]
+    init = gp.GaussianProcess.Parameters(gp.MeanParameters.zero, [gp.KernelParameters.se(3.0, 5.5), gp.KernelParameters.white(0.5)])
+    prior = [gp.GradDist.normal(1.0, 2.0), gp.GradDist.normal(1.5, 2.0), gp.GradDist.normal(-0.5, 2.0)]
+    m = np.eye(3)
+    old_f, old_g = gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode
+    gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode = gp.FORMULA_GPML, gp.GRAD_ANALYTIC
+    try:
+        chain = gp.KernelParameters.sampleHmc(observed, gp.Location.euclidean, init, prior, m, 4, 0.02, np.random.default_rng(5))
+        dev = [next(chain) for _ in range(8)]
+    finally:
+        gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode = old_f, old_g
+
+    def terms_of(v, f):
+        return [("se", f(v[0]), f(v[1])), ("white", f(v[2]))]
+
+    def ll(v):
+        return sum(pr.logPdf(a) for pr, a in zip(prior, v)) + oracle.loglik(xs, ys, terms_of(v, math.exp))["ll_gpml"]
+
+    def grad(v):
+        return oracle.mll_gradient(xs, ys, terms_of(v, float), mode="analytic") + np.array([pr.gradLogPdf(a) for pr, a in zip(prior, v)])
+
+    r2 = np.random.default_rng(5)
+    t = np.log([3.0, 5.5, 0.5])
+    ref = [t]
+    for _ in range(7):
+        t, _ = gp.Hmc.step(0.02, 4, m, ll, grad)(t, r2)
+        ref.append(t)
+    assert np.allclose(np.array(dev), np.array(ref), rtol=1e-7, atol=1e-9)
+    assert len({tuple(np.round(v, 12)) for v in dev}) > 2   # the chain moved

@@ -450,10 +450,25 @@ def extras_single_gpu(ctx, ds, G):
         return {"factor_plus_solve_ms": dt * 1e3, "evals_per_sec_factor_only_path": 1.0 / dt, "cores": os.cpu_count(),
                 "note": "LAPACK time excludes the covariance build"}
 
+    def c2_gradient():
+        """mllGradient at C2's size, 8 parameter vectors per call (log parameters)."""
+        import math
+        th = [[(0, math.log(3.0 + 0.1 * b), math.log(5.5)), (1, math.log(0.5), 0.0)] for b in range(BATCH)]
+        for _ in range(2):
+            ds.mll_gradient(th, mode=G.GRAD_ANALYTIC)
+        t0 = time.perf_counter(); g, info = ds.mll_gradient(th, mode=G.GRAD_ANALYTIC); w = time.perf_counter() - t0
+        t = ctx.last_timing()
+        n = float(N_TRAIN)
+        return {"batch": BATCH, "info": int(info.max()), "gradients_per_sec_e2e": BATCH / w, "build_ms": t[0],
+                "factor_and_inverse_rows_ms": t[1], "contraction_ms": t[2],
+                "factor_and_inverse_rows_tflops": BATCH * (2 * n ** 3 / 3) / (t[1] * 1e-3) * 1e-12,
+                "contraction_tflops": BATCH * (n ** 3 / 3) / (t[2] * 1e-3) * 1e-12}
+
     guarded("c1_example_mcmc_n300", c1)
     guarded("cpu_lapack_b2_n4096", cpu_lapack)
     guarded("c2_single_proposal_latency", latency)
     guarded("c2_predict_m4096", c2_predict)
+    guarded("c2_mll_gradient_batch8", c2_gradient)
     guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10))
     guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64, 8, 1, C5_TERMS, IG5, 5, -15, 15))
     guarded("c4", c4)

@@ -453,6 +453,7 @@ def extras_single_gpu(ctx, ds, G):
     def c2_gradient():
         """mllGradient at C2's size, 8 parameter vectors per call (log parameters)."""
         import math
+        BATCH = 8
         th = [[(0, math.log(3.0 + 0.1 * b), math.log(5.5)), (1, math.log(0.5), 0.0)] for b in range(BATCH)]
         for _ in range(2):
             ds.mll_gradient(th, mode=G.GRAD_ANALYTIC)

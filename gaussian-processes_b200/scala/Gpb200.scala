@@ -9,6 +9,7 @@
 //   KernelParameters.sample        KernelParameters.scala:231-246 -> unchanged (it calls loglikelihood)
 //   MeanParameters.samplePlane     MeanParameters.scala:74-103    -> Gpb200.samplePlane
 //   GaussianProcess.draw           GaussianProcess.scala:67-83    -> Gpb200.draw
+//   GaussianProcess.mllGradient    GaussianProcess.scala:166-187  -> Gpb200.mllGradient
 package com.github.jonnylaw.gp
 
 import java.lang.foreign._
@@ -181,5 +182,36 @@ object Gpb200 {
         1e-3, mu, z, out, info).asInstanceOf[Int])
       breeze.linalg.DenseVector(out.toArray(JAVA_DOUBLE))
     } finally a.close()
+  }
+  private val mllGradientH = fn("gpb_mll_gradient", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
+    ADDRESS, JAVA_INT, ADDRESS, JAVA_INT, JAVA_DOUBLE, JAVA_INT, ADDRESS, ADDRESS))
+
+  /** Same signature and currying as GaussianProcess.mllGradient (GaussianProcess.scala:166-169); p holds
+    * the unconstrained kernel parameters, as sampleHmc / sampleEhmc pass them.  mode 0 = the formulas
+    * the Scala executes, 1 = the analytic gradient in the log parameters. */
+  def mllGradient(observed: Vector[Data], dist: (Location[Double], Location[Double]) => Double,
+                  mode: Int = 0): Parameters => Array[Double] = {
+    requireEuclidean(dist)
+    val arena = Arena.ofShared()
+    val (x, dim) = soa(observed.map(_.x), arena)
+    val y = arena.allocateFrom(JAVA_DOUBLE, observed.map(_.y): _*)
+    val dsOut = arena.allocate(ADDRESS)
+    check(dsCreate.invoke(ctx.get, observed.size, dim, x, y, dsOut).asInstanceOf[Int])
+    val ds = dsOut.get(ADDRESS, 0)
+
+    { p: Parameters =>
+      val a = Arena.ofConfined()
+      try {
+        val beta = p.meanParameters.toList
+        val np = p.kernelParameters.map(_.toList.size).sum
+        val grad = a.allocate(JAVA_DOUBLE, np); val info = a.allocate(JAVA_INT)
+        check(mllGradientH.invoke(ctx.get, ds, 1, terms(p.kernelParameters, a), p.kernelParameters.size,
+          if (beta.isEmpty) MemorySegment.NULL else a.allocateFrom(JAVA_DOUBLE, beta: _*),
+          beta.size, 1e-3, mode, grad, info).asInstanceOf[Int])
+        if (info.get(JAVA_INT, 0) != 0) // kxx not positive definite: the LU of the reference would not notice
+          throw new breeze.linalg.NotConvergedException(breeze.linalg.NotConvergedException.Divergence)
+        grad.toArray(JAVA_DOUBLE)
+      } finally a.close()
+    }
   }
 }

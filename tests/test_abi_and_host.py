@@ -141,3 +141,48 @@ def test_design_matrix_mirrors_the_reference_layout():
     assert np.array_equal(X, np.array([[1, 1, 4], [1, 2, 5], [1, 3, 6.0]]))
     X1 = gp.MeanParameters.makeDesignMatrix([gp.One(7.0), gp.One(8.0)])
     assert np.array_equal(X1, np.array([[1, 7], [1, 8.0]]))
+
+
+def test_hmc_family_host_logic_on_a_toy_target():
+    """Hmc / DualAverage / Ehmc (Hmc.scala, DualAveraging.scala, Ehmc.scala) are host control flow around
+    two callbacks; checked here on a standard-normal target (no device): closed-form numbers, the
+    as-executed field permutation of DualAverage.step, and that the intended mode tunes and samples."""
+    import math
+    import warnings
+    import gpb200 as gp
+    pos = lambda t: -0.5 * float(np.sum(np.asarray(t) ** 2))
+    grad = lambda t: -np.asarray(t)
+    # one leapfrog on a harmonic oscillator, by hand
+    t1, p1 = gp.Hmc.leapfrog(0.1, grad, np.array([1.0]), np.array([0.0]))
+    assert np.allclose(t1, [1.0 - 0.005]) and np.allclose(p1, [-0.05 - 0.05 * 0.995])
+    assert gp.Hmc.kinetic([3.0, 4.0]) == 12.5
+    assert gp.Hmc.logAcceptance([float("nan")], [0.0], [0.0], [0.0], pos) == -math.inf
+    # updateEps, DualAveraging.scala:38-45 by hand for m = 4
+    hm, le, lb = gp.DualAverage.updateEps(4, 1.0, 0.65, 0.25)(0.1, 0.0, 0.5)
+    ra = 1 / 14.0
+    assert hm == (1 - ra) * 0.1 + ra * 0.4 and le == 1.0 - (2.0 * hm) / 0.05
+    assert lb == 4 ** -0.75 * le + (1 - 4 ** -0.75) * 0.5
+    assert gp.Ehmc.isUTurn([0.0, 0.0], [1.0, 0.0], [-1.0, 5.0]) and not gp.Ehmc.isUTurn([0.0], [1.0], [1.0])
+    s0 = gp.DualAverageState(1, np.array([0.3]), math.log(0.5), 0.0, 0.0)
+    old = (gp.DualAverage.as_executed, gp.Ehmc.as_executed)
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            gp.DualAverage.as_executed = True
+            s1 = gp.DualAverage.step(3, 0.0, np.eye(1), pos, grad)(s0, np.random.default_rng(0))
+            gp.DualAverage.as_executed = False
+            s2 = gp.DualAverage.step(3, 0.0, np.eye(1), pos, grad)(s0, np.random.default_rng(0))
+            assert (s1.logeps, s1.logepsbar, s1.hm) == (s2.hm, s2.logeps, s2.logepsbar)   # the positional mix-up
+            gp.Ehmc.as_executed = False
+            eps = gp.DualAverage.tuneStepsize(150, np.array([0.5, -0.3]), 5, np.eye(2), pos, grad, rng=np.random.default_rng(2))
+            assert 0.2 < eps < 4.0
+            ch = gp.Ehmc.sample(5, np.eye(2), pos, grad, 150, np.array([0.5, -0.3]), k=100, rng=np.random.default_rng(3))
+            xs = np.array([next(ch) for _ in range(1500)])
+            assert np.all(np.abs(xs.mean(0)) < 0.2) and np.all(np.abs(xs.std(0) - 1.0) < 0.2)
+            # as executed the tuner diverges and the chain stops moving (DESIGN.md)
+            gp.DualAverage.as_executed, gp.Ehmc.as_executed = True, True
+            ch = gp.Ehmc.sample(5, np.eye(2), pos, grad, 60, np.array([0.5, -0.3]), k=20, rng=np.random.default_rng(3))
+            xs = np.array([next(ch) for _ in range(20)])
+            assert np.allclose(xs, xs[0])
+    finally:
+        gp.DualAverage.as_executed, gp.Ehmc.as_executed = old

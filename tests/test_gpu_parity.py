@@ -529,3 +529,41 @@ def test_hmc_chain_follows_the_oracle_driven_chain(oracle):
         ref.append(t)
     assert np.allclose(np.array(dev), np.array(ref), rtol=1e-7, atol=1e-9)
     assert len({tuple(np.round(v, 12)) for v in dev}) > 2   # the chain moved
+
+
+def test_ehmc_device_driven_matches_oracle_driven(oracle):
+    """KernelParameters.sampleEhmc (KernelParameters.scala:171-198) in the intended mode: dual-averaging
+    warm-up, empirical leapfrog counts and the chain, once on the device calls and once on the oracle."""
+    import warnings
+    import gpb200 as gp
+    rng = np.random.default_rng(32)
+    n = 100
+    xs = np.sort(rng.uniform(-10, 10, n))
+    ys = np.linalg.cholesky(oracle.build_cov(xs, SE_W, 1e-3)) @ rng.standard_normal(n)
+    observed = [gp.GaussianProcess.Data(gp.One(float(a)), float(b)) for a, b in zip(xs, ys)]
+    init = gp.GaussianProcess.Parameters(gp.MeanParameters.zero, [gp.KernelParameters.se(3.0, 5.5), gp.KernelParameters.white(0.5)])
+    prior = [gp.GradDist.normal(1.0, 2.0), gp.GradDist.normal(1.5, 2.0), gp.GradDist.normal(-0.5, 2.0)]
+
+    def terms_of(v, f):
+        return [("se", f(v[0]), f(v[1])), ("white", f(v[2]))]
+
+    def ll(v):
+        return sum(pr.logPdf(a) for pr, a in zip(prior, v)) + oracle.loglik(xs, ys, terms_of(v, math.exp))["ll_gpml"]
+
+    def grad(v):
+        return oracle.mll_gradient(xs, ys, terms_of(v, float), mode="analytic") + np.array([pr.gradLogPdf(a) for pr, a in zip(prior, v)])
+
+    old = (gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode, gp.DualAverage.as_executed, gp.Ehmc.as_executed)
+    gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode = gp.FORMULA_GPML, gp.GRAD_ANALYTIC
+    gp.DualAverage.as_executed, gp.Ehmc.as_executed = False, False
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            chain = gp.KernelParameters.sampleEhmc(observed, gp.Location.euclidean, init, prior, 3, 4, rng=np.random.default_rng(9), k=5)
+            dev = np.array([next(chain) for _ in range(5)])
+            ref_chain = gp.Ehmc.sample(3, np.eye(3), ll, grad, 4, np.log([3.0, 5.5, 0.5]), k=5, rng=np.random.default_rng(9))
+            ref = np.array([next(ref_chain) for _ in range(5)])
+    finally:
+        gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode, gp.DualAverage.as_executed, gp.Ehmc.as_executed = old
+    assert np.all(np.isfinite(dev))
+    assert np.allclose(dev, ref, rtol=1e-6, atol=1e-8)

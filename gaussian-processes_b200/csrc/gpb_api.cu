@@ -66,7 +66,7 @@ int fill_hyper(Hyper* h, const gpb_term* terms, int nterms, const double* beta, 
 int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y,
                const double* d_xstar, double nugget) {
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-  launch_build(ctx->stream, g, d_x, d_y, d_xstar, ctx->hyper, nugget, ctx->mats, 0, 0);
+  launch_build(ctx->stream, g, d_x, d_y, d_xstar, ctx->hyper, nugget, ctx->mats, BUILD_FAST, 0);
   ctx->launches += 1;
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   int rc = do_chol(ctx, g, 0);

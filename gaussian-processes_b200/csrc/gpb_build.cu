@@ -35,7 +35,23 @@ __device__ __forceinline__ double cov_of_dist(const Hyper& h, double d) {
   return s;
 }
 
-// mode 0: covariance system (lower trapezoid only unless full != 0); mode 1: distance matrix.
+// Hot-path form of the same sum: exp(d2 * (-1/s^2)) with -1/s^2 formed once per CTA -- no square
+// root, no re-squaring, no IEEE division per entry (k_build is FP64-ALU bound on exactly those).  d2 is
+// within an ulp of sqrt(d2)^2, so an entry moves by at most a few ulps of the term's scale h:
+// |dk| <= h x e^-x 2^-52 with x = d^2/s^2, i.e. < 0.4 ulp(h) -- five orders below the 1e-10 tolerance
+// of the log-likelihood.  The matrix-level gpb_build_cov keeps the reference's exact operation order.
+__device__ __forceinline__ double cov_of_dist2_fast(const Hyper& h, const double* __restrict__ ninv2, double d2) {
+  double s = 0.0;
+#pragma unroll 1
+  for (int t = 0; t < h.nterms; ++t) {
+    const double v = (h.kind[t] == GPB_KIND_SE) ? h.p0[t] * exp(d2 * ninv2[t]) : ((d2 == 0.0) ? h.p0[t] : 0.0);
+    s = __dadd_rn(s, v);
+  }
+  return s;
+}
+
+// mode 0: covariance system, the reference's exact operation order (lower trapezoid only unless
+// full != 0); mode 1: distance matrix; mode 2: covariance system, hot-path form (cov_of_dist2_fast).
 __global__ void __launch_bounds__(256)
 k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         const double* __restrict__ xstar, const Hyper* __restrict__ hyper, double nugget,
@@ -59,9 +75,11 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
   const int b = blockIdx.y;
   __shared__ double rx[2][TILE], cx[2][TILE], cy[TILE], cm[TILE];
   __shared__ Hyper h;
+  __shared__ double ninv2[MAXT];
   const int tid = threadIdx.x;
   if (tid == 0) h = hyper[b];
   __syncthreads();
+  if (tid < MAXT) ninv2[tid] = (tid < h.nterms && h.kind[tid] == GPB_KIND_SE) ? -1.0 / (h.p1[tid] * h.p1[tid]) : 0.0;
   if (tid < TILE) {
     // column entities are always training points (or padding)
     int c = tj * TILE + tid;
@@ -118,12 +136,17 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
         double dy = r1 - cx[1][cl];
         d2 = __dadd_rn(d2, __dmul_rn(dy, dy));  // no FMA contraction: mirror Location.scala:30-31
       }
-      double d = sqrt(d2);  // Location.scala:28-31
-      if (mode == 1) {
-        v = d;
+      if (mode == 2) {
+        v = cov_of_dist2_fast(h, ninv2, d2);
+        if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);
       } else {
-        v = cov_of_dist(h, d);
-        if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);  // GaussianProcess.scala:117-118
+        double d = sqrt(d2);  // Location.scala:28-31
+        if (mode == 1) {
+          v = d;
+        } else {
+          v = cov_of_dist(h, d);
+          if (rclass == 0 && R == Cc) v = __dadd_rn(v, nugget);  // GaussianProcess.scala:117-118
+        }
       }
     } else if (rclass == 5) {
       // design-matrix column (MeanParameters.scala:55-65), or a row of the identity block

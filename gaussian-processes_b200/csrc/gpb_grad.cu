@@ -327,7 +327,7 @@ extern "C" int gpb_mll_gradient(gpb_ctx* ctx, const gpb_dataset* ds, int batch, 
   CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper) * batch, cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaMemcpyAsync(d_spec, specs.data(), sizeof(GradSpec) * batch, cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-  launch_build(ctx->stream, g, ds->x, ds->y, nullptr, ctx->hyper, nugget, ctx->mats, 0, 0, nullptr);
+  launch_build(ctx->stream, g, ds->x, ds->y, nullptr, ctx->hyper, nugget, ctx->mats, BUILD_FAST, 0, nullptr);
   ctx->launches += 1;
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   if ((rc = do_chol(ctx, g, 0))) return rc;

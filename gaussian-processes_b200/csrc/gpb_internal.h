@@ -10,6 +10,9 @@ struct SchedState {
   int error;      // != 0: a watchdog fired (GPB_E_WATCHDOG); kernels drain without waiting
 };
 
+// k_build modes: the reference's exact operation order (matrix-level gpb_build_cov), the distance
+// matrix, and the hot-path form used by every factorising entry point (gpb_build.cu).
+constexpr int BUILD_EXACT = 0, BUILD_DISTANCE = 1, BUILD_FAST = 2;
 void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
                   const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
                   int full, const double* rows = nullptr);

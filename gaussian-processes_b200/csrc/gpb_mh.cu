@@ -284,7 +284,7 @@ int gpb_mh_run(gpb_ctx* ctx, const gpb_dataset* ds, int chains, int iters, const
   CK(cudaEventRecord(ctx->ev[1], st));
   for (int it = -1; it < iters; ++it) {
     k_mh_propose<<<gb, tb, 0, st>>>(md, it, d_cur, d_z, d_prop, ctx->hyper);
-    launch_build(st, g, ds->x, ds->y, nullptr, ctx->hyper, opts->nugget, ctx->mats, 0, 0);
+    launch_build(st, g, ds->x, ds->y, nullptr, ctx->hyper, opts->nugget, ctx->mats, BUILD_FAST, 0);
     ctx->launches += 2;
     if ((rc = do_chol(ctx, g, 0))) return rc;
     launch_ll_epilogue(st, g, ctx->mats, ctx->info, ctx->ll);

@@ -24,7 +24,7 @@ int gpb_plane_stats(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, 
   CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper), cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaMemcpyAsync(d_rows, X, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-  launch_build(ctx->stream, g, ds->x, ds->y, nullptr, ctx->hyper, nugget, ctx->mats, 0, 0, d_rows);
+  launch_build(ctx->stream, g, ds->x, ds->y, nullptr, ctx->hyper, nugget, ctx->mats, BUILD_FAST, 0, d_rows);
   ctx->launches += 1;
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   if ((rc = do_chol(ctx, g, 0))) return rc;
@@ -121,7 +121,7 @@ int gpb_draw(gpb_ctx* ctx, int n, int dim, const double* x, const gpb_term* term
   if (mu) CK(cudaMemcpyAsync(d_mu, mu, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
   else CK(cudaMemsetAsync(d_mu, 0, sizeof(double) * n, ctx->stream));
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-  launch_build(ctx->stream, g, d_x, nullptr, nullptr, ctx->hyper, nugget, ctx->mats, 0, 0);
+  launch_build(ctx->stream, g, d_x, nullptr, nullptr, ctx->hyper, nugget, ctx->mats, BUILD_FAST, 0);
   ctx->launches += 1;
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   if ((rc = do_chol(ctx, g, 0))) return rc;

@@ -59,7 +59,7 @@ constexpr int AT_STAGES = TILE / SCOLS;  // stages that carry the task's own til
 static_assert(SCOLS == 32 && AT_STAGES == 2, "each consumer warp's 32 columns of the tile sit in one stage");
 static_assert(STAGES >= AT_STAGES + 2, "ring too small");
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
-constexpr int TRACE_SLOTS = 10;
+constexpr int TRACE_SLOTS = 14;   // == CHOL_TRACE_SLOTS
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 
 struct __align__(128) CholSmem {
@@ -87,6 +87,8 @@ struct TaskDesc { int b, i, j; };
 // [0] globaltimer at receipt, [1] clock at receipt, [2] first stage landed, [3] contraction done,
 // [4] dependency on the diagonal block satisfied, [5] factor / solve done, [6] clock at release,
 // [7] globaltimer at release, [8] main-loop stages that were not ready at first probe, [9] cycles the main loop spent blocked on stage data.
+// Producer lane (same SM, same clock): [10] ticket posted, [11] the task's own tile issued, [12] last
+// contraction stage issued, [13] L_jj^-T stages issued (or scratch granted).
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long v;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
@@ -397,16 +399,19 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     RelState rs; rs.r = 0;
     int posted = 0;   // tasks handed to the consumers that will post a publication
     // the next ticket is drawn while the current task's last stages are still in flight (after its
-    // contraction stages are issued, before its solve stages), so the atomic's latency is hidden
+    // contraction stages are issued, before its solve stages), so the atomic's latency is hidden.
+    // Drawing it earlier (at the start of the task) was measured and is worse for chain-bound launches:
+    // a busy CTA then holds a critical-path task in its own queue (n=1024 batch 32: 0.64 -> 0.72 ms).
     auto fetch = [&]() {
       int tn;
       if (static_sched) { tn = static_next; static_next += gridDim.x; }
       else tn = task_begin + atomicAdd(&sched->next_task, 1);
-      return tn >= task_end ? -1 : tn;
+      return tn;   // raw: clamped at the loop top
     };
     int t_next = (lane == 0) ? fetch() : 0;
     for (;;) {
       int t = __shfl_sync(0xffffffffu, t_next, 0);
+      if (t >= task_end) t = -1;
       const int slot = q & 1, qpar = (q >> 1) & 1;
       if (lane == 0) {
         if (!mbar_wait_serving(&sm.tq_empty[slot], qpar ^ 1, sm, rs)) atomicExch(&sched->error, 2);
@@ -423,6 +428,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       }
       if (!solve_only) ++posted;
       const int* done_b = done + (size_t)d.b * g.rt;
+      unsigned long long* ptr_ = (TRACE && trace != nullptr && lane == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
+      if (ptr_) ptr_[10] = clock64();
       if (lane == 0) {
         // the tile itself (accumulator start value) comes first, as AT_STAGES ordinary stages:
         // stage s holds tile columns s*SCOLS .. in [column][LDT] order
@@ -435,6 +442,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col + KC, d.b, &sm.full[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        if (ptr_) ptr_[11] = clock64();
         // one elected lane drives the ring: two TMA boxes per stage ({LDT rows x KC cols}: the
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
         // progress counters only grow: poll again only when the last value seen is not enough
@@ -455,6 +463,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
+        if (ptr_) ptr_[12] = clock64();
         t_next = fetch();
         if (d.i != d.j) {
           // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
@@ -479,6 +488,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
+        if (ptr_) ptr_[13] = clock64();
       }
       __syncwarp();
     }

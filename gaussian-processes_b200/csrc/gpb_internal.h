@@ -26,7 +26,7 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done,
                 int* info, SchedState* sched, int mode, int num_sms, int solve_only = 0,
                 unsigned long long* trace = nullptr);
-constexpr int CHOL_TRACE_SLOTS = 10;
+constexpr int CHOL_TRACE_SLOTS = 14;
 long long chol_task_count(const Geom& g);
 // solve_only: the top square already holds a lower-triangular factor; only the appended rows are
 // solved (X = B L^-T) -- the matrix-level forward / backward substitutions.

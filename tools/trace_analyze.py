@@ -61,6 +61,9 @@ def main():
         print("   dep ok->compute done  us: p50 %.2f  p90 %.2f" % tuple(np.percentile(us(t[:, 5] - t[:, 4]), [50, 90])))
         print("   compute done->release us: p50 %.2f  p90 %.2f" % tuple(np.percentile(us(t[:, 6] - t[:, 5]), [50, 90])))
         print("   total task us: mean %.2f" % us(t[:, 6] - t[:, 1]).mean())
+        print("   producer: posted->recv us p50 %.2f | tile issued - recv p50 %.2f p90 %.2f | last C stage issued -> mainloop end p50 %.2f | LT issued - mainloop end p50 %.2f p90 %.2f" % (
+            np.median(us(t[:, 1] - t[:, 10])), *np.percentile(us(t[:, 11] - t[:, 1]), [50, 90]),
+            np.median(us(t[has, 3] - t[has, 12])), *np.percentile(us(t[:, 13] - t[:, 3]), [50, 90])))
     # busy fraction per SM
     span = (tr[:, 7].max() - g0) / 1e3
     busy = us(tr[:, 6] - tr[:, 1]).sum()

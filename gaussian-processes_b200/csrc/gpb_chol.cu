@@ -81,7 +81,13 @@ long long chol_task_count(const Geom& g) {
   return (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
 }
 
-struct TaskDesc { int b, i, j; };
+// Task kinds.  The diagonal block j+1 is not a task of its own: its contraction over the block columns
+// k < j is pre-accumulated off the critical path (K_PART, stored back in place), and the CTA that
+// solves tile (j+1, j) keeps X in shared memory, applies the last update X X^T and factors the block
+// on the spot (K_FUSED) -- the dependency chain diag(j) -> (j+1, j) -> diag(j+1) loses one publication,
+// one acquire and one TMA round trip per block column.  Summation order is unchanged.
+enum : int { K_PLAIN = 0, K_DIAG0 = 1, K_PART = 2, K_FUSED = 3 };
+struct TaskDesc { int b, i, j, kind; };
 
 // Optional per-task trace (debug builds of the schedule analysis; trace == nullptr in production):
 // [0] globaltimer at receipt, [1] clock at receipt, [2] first stage landed, [3] contraction done,
@@ -103,9 +109,12 @@ __device__ __forceinline__ unsigned int smid() {
 // Ticket order (topological; chosen so the next diagonal block is factored while the bulk of the
 // current block column is still being solved):
 //   group -1 : diag(0,0) of every proposal
-//   group  j : A  (j+1, j)      the tile the next diagonal block depends on      [if j+1 < rt]
-//              B  diag(j+1,j+1)                                                  [if j+1 < nt]
+//   group  j : B  (j+1, j+1)    partial accumulation over k < j, stored back (K_PART)   [if j+1 < nt]
+//              A  (j+1, j)      solve, then the update and factorisation of diag(j+1)
+//                               (K_FUSED; a plain solve when row j+1 is an appended row)  [if j+1 < rt]
 //              C  (i, j), i >= j+2
+//   (triangular-solve mode keeps the older meaning of the two slots: B inverts the given diagonal
+//   block, A is void)
 // tickets before group j (j <= nt-1):  batch * (1 + j*rt - j(j+1)/2 + j)
 __device__ __host__ __forceinline__ long long group_start(int batch, int rt, int j) {
   return (long long)batch * (1 + (long long)j * rt - (long long)j * (j + 1) / 2 + j);
@@ -121,16 +130,17 @@ __device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcach
   t -= gi * per_group;
   const int b0 = gi * g.tgroup;
   const int gb = min(g.tgroup, g.batch - b0);
-  if (t < gb) { d.b = b0 + t; d.i = 0; d.j = 0; return d; }
+  d.kind = K_PLAIN;
+  if (t < gb) { d.b = b0 + t; d.i = 0; d.j = 0; d.kind = K_DIAG0; return d; }
   while (jcache + 1 < g.nt && (long long)t >= group_start(gb, g.rt, jcache + 1)) ++jcache;
   while (jcache > 0 && (long long)t < group_start(gb, g.rt, jcache)) --jcache;
   const int j = jcache;
   int local = t - (int)group_start(gb, g.rt, j);
   const int nA = (j + 1 < g.rt) ? gb : 0, nB = (j + 1 < g.nt) ? gb : 0;
-  if (local < nA) { d.b = b0 + local; d.i = j + 1; d.j = j; return d; }
-  local -= nA;
-  if (local < nB) { d.b = b0 + local; d.i = j + 1; d.j = j + 1; return d; }
+  if (local < nB) { d.b = b0 + local; d.i = j + 1; d.j = j + 1; d.kind = K_PART; return d; }
   local -= nB;
+  if (local < nA) { d.b = b0 + local; d.i = j + 1; d.j = j; d.kind = (j + 1 < g.nt) ? K_FUSED : K_PLAIN; return d; }
+  local -= nA;
   const int per = g.rt - j - 2;
   d.b = b0 + local / per; d.i = j + 2 + local % per; d.j = j;
   return d;
@@ -422,12 +432,16 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       if (t < 0) break;
       const TaskDesc d = decode_task(g, t, jcache);
       const int k0 = task_k0(g, d);
-      if ((solve_only && d.i < g.nt) || k0 < 0) {   // L is given: no accumulation for top-square tiles; void task
+      const int kind = solve_only ? K_PLAIN : d.kind;
+      // L is given: no accumulation for top-square tiles; void task; nothing to pre-accumulate for block 1
+      if ((solve_only && d.i < g.nt) || k0 < 0 || (kind == K_PART && d.j == 1)) {
         if (lane == 0) t_next = fetch();
         continue;
       }
-      if (!solve_only) ++posted;
+      if (!solve_only) posted += (kind == K_FUSED) ? 2 : 1;
+      const int kend = (kind == K_PART) ? d.j - 1 : d.j;   // K_PART leaves the last block column to K_FUSED
       const int* done_b = done + (size_t)d.b * g.rt;
+      const int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
       unsigned long long* ptr_ = (TRACE && trace != nullptr && lane == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
       if (ptr_) ptr_[10] = clock64();
       if (lane == 0) {
@@ -447,7 +461,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         // 4 extra rows give the padded, bank-conflict-free smem pitch for free)
         // progress counters only grow: poll again only when the last value seen is not enough
         int seen_i = 0, seen_j = 0;
-        for (int kc = k0; kc < d.j; ++kc) {
+        for (int kc = k0; kc < kend; ++kc) {
           bool polled = false;
           if (seen_i < kc + 1) { seen_i = wait_counter_serving(done_b + d.i, kc + 1, &sched->error, sm, rs); polled = true; }
           if (seen_j < kc + 1) { seen_j = wait_counter_serving(done_b + d.j, kc + 1, &sched->error, sm, rs); polled = true; }
@@ -465,7 +479,9 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         }
         if (ptr_) ptr_[12] = clock64();
         t_next = fetch();
-        if (d.i != d.j) {
+        if (kind == K_PART) {
+          // nothing more to stream: the consumers store the partial sum back in place
+        } else if (d.i != d.j) {
           // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
           // ring: LT_STAGES stages of SCOLS rows each, as soon as diag(j) is published
           if (seen_j < d.j + 1) wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
@@ -478,6 +494,27 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             tma_load_2d(&sm.stage[stage][0], &tmapL, 0, row0 + s * SCOLS, &sm.full[stage]);
             tma_load_2d(&sm.stage[stage][KC * LDT], &tmapL, 0, row0 + s * SCOLS + KC, &sm.full[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          if (kind == K_FUSED) {
+            // ... followed by the pre-accumulated diagonal block (d.i, d.i) and the scratch stages of
+            // its factorisation
+            if (d.j > 0) wait_counter_serving(part_b + d.i, 1, &sched->error, sm, rs);
+            fence_proxy_async();
+#pragma unroll 1
+            for (int s = 0; s < AT_STAGES; ++s) {
+              if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+              mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+              const int col = d.i * TILE + s * SCOLS;
+              tma_load_3d(&sm.stage[stage][0], &tmap, d.i * TILE, col, d.b, &sm.full[stage]);
+              tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col + KC, d.b, &sm.full[stage]);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+#pragma unroll 1
+            for (int s = 0; s < LT_STAGES; ++s) {
+              if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+              mbar_arrive(&sm.full[stage]);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
           }
         } else if (!solve_only) {
           // diagonal task: grant LT_STAGES empty stages as scratch for the stacked inverse rows
@@ -530,9 +567,12 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); }
     const TaskDesc d = decode_task(g, t, jcache);
     const int k0 = task_k0(g, d);
-    if (k0 < 0) continue;
+    const int kind = solve_only ? K_PLAIN : d.kind;
+    if (k0 < 0 || (kind == K_PART && d.j == 1)) continue;
+    const int kend = (kind == K_PART) ? d.j - 1 : d.j;
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
+    int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
     double* Aij = M + (size_t)(d.j * TILE) * g.ld + (size_t)d.i * TILE;  // (r, c) at Aij[c*ld + r]
     if (solve_only && d.i < g.nt && d.i != d.j) {
       // triangular-solve mode: the factor is an input, its off-diagonal tiles are already final
@@ -586,7 +626,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       }
     };
 
-    const int nstage = (solve_only && d.i < g.nt) ? 0 : (d.j - k0) * (TILE / KC);
+    const int nstage = (solve_only && d.i < g.nt) ? 0 : (kend - k0) * (TILE / KC);
     // Stage release is DELAYED by one stage: ptxas schedules mbarrier.arrive right behind the last
     // LDS of a stage without waiting for those loads to return, and with two CTAs per SM the
     // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
@@ -642,6 +682,23 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     }
 
     if (tr) { tr[3] = clock64(); tr[8] = (unsigned long long)not_ready; tr[9] = 0; }
+    if (kind == K_PART) {
+      // ---------- pre-accumulated diagonal block: back to its place, K_FUSED takes it from there ----------
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) {
+          const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+          *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + r) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+        }
+      __syncwarp();                      // the stores consumed every accumulator: all LDS of the ring are done
+      release_pre();
+      if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
+      if (tr) { tr[4] = tr[5] = clock64(); }
+      post_release(part_b + d.i, 1);
+      if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
+      continue;
+    }
     // acc -> Cs (column-major [c][r])
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt)
@@ -655,8 +712,27 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     release_pre();
     if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);  // accumulators are stored: all reads done
 
+    // Cs holds a diagonal block: factor it (diag_factor: thread = one of the 128 rows of the stacked
+    // [Cs; I]) in LT_STAGES scratch stages the producer grants, report a bad pivot, publish the block.
+    auto factor_block = [&](int dj, double* Ajj, double* LTj) {
+      const int s0 = (int)stage;
+#pragma unroll 1
+      for (int s = 0; s < LT_STAGES; ++s) {
+        wait_full(stage, phase);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      diag_factor(sm, s0, Ajj, LTj, g.ld, tid);
+      bar_named(1, NCONS);             // bad_col is final; every read of the scratch stages is done
+      if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, dj * TILE + sm.bad_col + 1);  // 1-based pivot
+      post_release(done_b + dj, dj + 1);
+      fence_proxy_async();             // generic writes to the scratch stages before TMA refills them
+      __syncwarp();
+      if (lane == 0)
+        for (int s = 0; s < LT_STAGES; ++s) mbar_arrive(&sm.empty[(s0 + s) % STAGES]);
+    };
+
     if (d.i == d.j) {
-      // ---------- diagonal task: factor the stacked [acc; I]; thread = one of its 128 rows ----------
+      // ---------- diagonal task (block 0, or the given factor of the triangular-solve mode) ----------
       double* LTj = linvt + ((size_t)d.b * g.nt + d.j) * (TILE * LDT);
       if (tr) tr[4] = clock64();
       if (solve_only) {
@@ -667,21 +743,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         bar_named(1, NCONS);
         if (tid == 0) atomicMax(done_b + d.j, d.j + 1);
       } else {
-        const int s0 = (int)stage;     // first of the LT_STAGES scratch stages the producer grants
-#pragma unroll 1
-        for (int s = 0; s < LT_STAGES; ++s) {
-          wait_full(stage, phase);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        }
-        diag_factor(sm, s0, Aij, LTj, g.ld, tid);
+        factor_block(d.j, Aij, LTj);
         if (tr) tr[5] = clock64();
-        bar_named(1, NCONS);           // bad_col is final; every read of the scratch stages is done
-        if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, d.j * TILE + sm.bad_col + 1);  // 1-based pivot
-        post_release(done_b + d.j, d.j + 1);
-        fence_proxy_async();           // generic writes to the scratch stages before TMA refills them
-        __syncwarp();
-        if (lane == 0)
-          for (int s = 0; s < LT_STAGES; ++s) mbar_arrive(&sm.empty[(s0 + s) % STAGES]);
       }
       if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     } else {
@@ -692,21 +755,22 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       constexpr int CT = SCOLS / 8;          // 8-column tiles of X per stage
       constexpr int CTW = CT / (CW / 4);     // ... per warp
       const int rq = warp & 3, ch = warp >> 2;
-#pragma unroll 1
+      double xs[LT_STAGES][CTW][2][2];       // X stays in registers: K_FUSED needs it again (s loop unrolled)
+#pragma unroll
       for (int s = 0; s < LT_STAGES; ++s) {
         wait_full(stage, phase);
         if (tr && s == 0) tr[4] = clock64();
         const double* LTs = &sm.stage[stage][ch * CTW * 8 * LDT];
-        double x[CTW][2][2];
+        double (&x)[CTW][2][2] = xs[s];
 #pragma unroll
         for (int ct = 0; ct < CTW; ++ct)
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
-        const int kend = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
-        const int kfull = kend - (CTW - 1) * 8;   // below this every column tile of the warp is live
+        const int kmax = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
+        const int kfull = kmax - (CTW - 1) * 8;   // below this every column tile of the warp is live
 #pragma unroll 2
-        for (int k0 = 0; k0 < kfull; k0 += 4) {
-          const int k = k0 + tq;
+        for (int kb = 0; kb < kfull; kb += 4) {
+          const int k = kb + tq;
           double a[CTW], bb[2];
 #pragma unroll
           for (int ct = 0; ct < CTW; ++ct) a[ct] = LTs[(ct * 8 + gq) * LDT + k];
@@ -753,7 +817,67 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         bar_named(1, NCONS);
         if (tid == 0) st_release(done_b + d.i, d.j + 1);
       } else {
+        // X is published; the barrier inside also says every warp is done with Cs (as C) and with L_jj^-T
         post_release(done_b + d.i, d.j + 1);
+      }
+      if (kind == K_FUSED) {
+        // ---------- ... and straight on to diag(d.i): block -= X X^T from shared memory, factor ----------
+        // X -> Cs in the panel layout of one 64-column chunk ([k = c][r], pitch LDT)
+#pragma unroll
+        for (int s = 0; s < LT_STAGES; ++s)
+#pragma unroll
+          for (int ct = 0; ct < CTW; ++ct)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+              const int c = s * SCOLS + (ch * CTW + ct) * 8 + gq, r = rq * 16 + nt * 8 + 2 * tq;
+              *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(xs[s][ct][nt][0], xs[s][ct][nt][1]);
+            }
+        // the pre-accumulated block arrives like every task's own tile
+        pre0 = (int)stage;
+        wait_full(stage, phase);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        pre1 = (int)stage;
+        wait_full(stage, phase);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        {
+          const double* T = &sm.stage[wc == 0 ? pre0 : pre1][0];
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NTW; ++nt) {
+              const double2 v = *reinterpret_cast<const double2*>(&T[(mt * 8 + gq) * LDT + wr * RW + nt * 8 + 2 * tq]);
+              acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
+            }
+        }
+        bar_named(1, NCONS);             // X is complete in Cs
+        // same k order as the streamed chunk it replaces (16 k-steps of 4): bitwise the same block
+#pragma unroll 4
+        for (int ks = 0; ks < TILE / 4; ++ks) {
+          const int k = ks * 4 + tq;
+          double a[4], bb[NTW];
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt) a[mt] = -sm.Cs[k * LDT + wc * 32 + mt * 8 + gq];
+#pragma unroll
+          for (int nt = 0; nt < NTW; ++nt) bb[nt] = sm.Cs[k * LDT + wr * RW + nt * 8 + gq];
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+        }
+        __syncwarp();
+        release_pre();
+        bar_named(1, NCONS);             // every warp has read X: Cs may take the block
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < NTW; ++nt) {
+            const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+            *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+          }
+        if (tid == 0) sm.bad_col = -1;
+        bar_named(1, NCONS);
+        factor_block(d.i, M + (size_t)(d.i * TILE) * g.ld + (size_t)d.i * TILE,
+                     linvt + ((size_t)d.b * g.nt + d.i) * (TILE * LDT));
       }
       if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
     }
@@ -813,7 +937,8 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   CUtensorMap tmapL;
   if (!make_tmap_linvt(&tmapL, g, linvt)) return -1;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
-  cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * g.rt, st);
+  // done [batch][rt] progress counters, followed by part [batch][nt] "diagonal block pre-accumulated" flags
+  cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * (g.rt + g.nt), st);
   cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
   int launches = 0;
   if (g.ident0 >= 0) {
@@ -856,7 +981,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
       long long begin = group_start(g.batch, g.rt, j);
       const long long nA = (j + 1 < g.rt) ? g.batch : 0, nB = (j + 1 < g.nt) ? g.batch : 0;
       const long long nC = (long long)g.batch * (g.rt - j - 2 > 0 ? g.rt - j - 2 : 0);
-      run(begin, nA); run(begin + nA, nB); run(begin + nA + nB, nC);
+      run(begin, nB); run(begin + nB, nA); run(begin + nA + nB, nC);
     }
   }
   return launches;

@@ -18,7 +18,8 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
                   int full, const double* rows = nullptr);
 
 // Tile Cholesky + panel solves of the tall system (gpb_chol.cu).
-//   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final)
+//   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final), followed by
+//          [batch][nt]  flags "diagonal block pre-accumulated over all but its last block column"
 //   linvt  [batch][nt][TILE][LDT]  inverse-transposes of the diagonal blocks (side output, pitch LDT)
 //   info   [batch]      first non-positive pivot (1-based, LAPACK) or 0
 // mode 0: one persistent launch over all tasks; mode 1: two launches per block column.

@@ -1,4 +1,4 @@
 #!/bin/bash
-python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "loglik_parity or schedulers or full_size_c2 or full_size_c3 or mh_ or predict" 2>&1 | tail -3
-python tools/c3_breakdown.py 2>&1 | head -8
-python tools/trace_analyze.py 4096 8 2>&1 | grep -A12 "offdiag" | grep "dep ok\|producer"
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -6
+timeout 200 python tools/latency_probe.py 2>&1 | tail -8
+timeout 300 python tools/c3_breakdown.py 2>&1 | head -9

@@ -16,15 +16,16 @@ def decode(batch, nt, rt, t):
     return (b + gi * G, i, j)
 
 def decode1(batch, nt, rt, t):
+    # ticket order of gpb_chol.cu: group j = [partial diag(j+1)] [fused (j+1, j) + diag(j+1)] [plain (i, j)]
     if t < batch: return (t, 0, 0)
     j = 0
     while j + 1 < nt and t >= gs(batch, rt, j + 1): j += 1
     local = t - gs(batch, rt, j)
     nA = batch if j + 1 < rt else 0; nB = batch if j + 1 < nt else 0
-    if local < nA: return (local, j + 1, j)
-    local -= nA
     if local < nB: return (local, j + 1, j + 1)
     local -= nB
+    if local < nA: return (local, j + 1, j)
+    local -= nA
     per = rt - j - 2
     return (local // per, j + 2 + local % per, j)
 
@@ -48,7 +49,8 @@ def main():
     isdiag = dec[:, 1] == dec[:, 2]
     g0 = tr[:, 0].min()
     us = lambda a: a / (ghz * 1e3)
-    for name, m in (("diag", isdiag), ("offdiag", ~isdiag)):
+    fused = (dec[:, 1] == dec[:, 2] + 1) & (dec[:, 1] < nt)
+    for name, m in (("diag block 0 / partial diag", isdiag), ("fused (j+1,j)+diag(j+1)", fused), ("plain offdiag", ~isdiag & ~fused)):
         t = tr[m]; j = dec[m, 2]
         has = j > 0
         print(f"--- {name}: {m.sum()} tasks")

@@ -155,9 +155,22 @@ __device__ __forceinline__ int task_k0(const Geom& g, const TaskDesc& d) {
   if (I >= g.nt) return 0;   // the rhs rows behind the identity block are dense
   return d.j < I ? -1 : I;
 }
-__global__ void k_preset_ident_done(Geom g, int* __restrict__ done) {
-  const int I = blockIdx.x * blockDim.x + threadIdx.x;
-  if (I < g.nt) done[(size_t)blockIdx.y * g.rt + g.ident0 + I] = I;
+// One launch instead of three memsets (+ a preset): zero the progress counters and flags, info and the
+// ticket counter (`error` stays sticky until the host has read it); preset done[i] = I for the rows of
+// an appended identity block.
+__global__ void k_chol_reset(Geom g, int* __restrict__ done, int* __restrict__ info, SchedState* sched) {
+  const int per = g.rt + g.nt;               // done [batch][rt] followed by part [batch][nt]
+  const long long total = (long long)g.batch * per;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    int v = 0;
+    if (g.ident0 >= 0 && i < (long long)g.batch * g.rt) {
+      const int row = (int)(i % g.rt);
+      if (row >= g.ident0 && row - g.ident0 < g.nt) v = row - g.ident0;
+    }
+    done[i] = v;
+    if (i < g.batch) info[i] = 0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) sched->next_task = 0;
 }
 
 __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* error) {
@@ -937,15 +950,13 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   CUtensorMap tmapL;
   if (!make_tmap_linvt(&tmapL, g, linvt)) return -1;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
-  // done [batch][rt] progress counters, followed by part [batch][nt] "diagonal block pre-accumulated" flags
-  cudaMemsetAsync(done, 0, sizeof(int) * (size_t)g.batch * (g.rt + g.nt), st);
-  cudaMemsetAsync(info, 0, sizeof(int) * (size_t)g.batch, st);
   int launches = 0;
-  if (g.ident0 >= 0) {
-    k_preset_ident_done<<<dim3((g.nt + 127) / 128, g.batch), 128, 0, st>>>(g, done);
+  {
+    const long long total = (long long)g.batch * (g.rt + g.nt);
+    const int blocks = (int)((total + 255) / 256 < 296 ? (total + 255) / 256 : 296);
+    k_chol_reset<<<blocks, 256, 0, st>>>(g, done, info, sched);
     ++launches;
   }
-  cudaMemsetAsync(&sched->next_task, 0, sizeof(int), st);  // `error` stays sticky until read
   if (mode == 0) {
     // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; single small proposals
     // are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA that

@@ -159,6 +159,11 @@ long long gpb_get_trace(gpb_ctx* ctx, unsigned long long* out, long long max_tas
     cudaMemcpy(out, ctx->trace, sizeof(unsigned long long) * nt * CHOL_TRACE_SLOTS, cudaMemcpyDeviceToHost);
   return ctx->trace_tasks;
 }
+long long gpb_schedule_task(int n, int appended, int batch, long long ticket, int* out4) {
+  if (n < 1 || appended < 0 || batch < 1) return GPB_E_INVALID;
+  const Geom g = make_geom(n, 1, appended, false, batch);
+  return chol_schedule_task(g, ticket, out4);
+}
 int gpb_set_sched(gpb_ctx* ctx, int mode) {
   if (!ctx || mode < 0 || mode > 1) return GPB_E_INVALID;
   ctx->sched_mode = mode;

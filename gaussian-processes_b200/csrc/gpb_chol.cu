@@ -122,7 +122,7 @@ __device__ __host__ __forceinline__ long long group_start(int batch, int rt, int
 // Tickets are dealt out proposal-group by proposal-group (g.tgroup proposals per group, each group
 // in the column order above): the panels a group streams stay L2-resident, and the tail of one
 // group overlaps the head of the next.
-__device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcache) {
+__host__ __device__ __forceinline__ TaskDesc decode_task(const Geom& g, int t, int& jcache) {
   TaskDesc d;
   const int per_mat = g.nt * g.rt - g.nt * (g.nt - 1) / 2;
   const int per_group = g.tgroup * per_mat;
@@ -937,6 +937,19 @@ bool make_tmap(CUtensorMap* tm, const Geom& g, double* mats) {
   return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, mats, dims, strides, box, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// Host-side view of the ticket order (the same decode_task the kernel runs): schedule introspection
+// for the tests and the trace tools.
+long long chol_schedule_task(const Geom& g_in, long long ticket, int* out4) {
+  Geom g = g_in;
+  if (g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;
+  const long long total = chol_task_count(g);
+  if (ticket < 0 || ticket >= total || !out4) return total;
+  int jcache = 0;
+  const TaskDesc d = decode_task(g, (int)ticket, jcache);
+  out4[0] = d.b; out4[1] = d.i; out4[2] = d.j; out4[3] = d.kind;
+  return total;
 }
 
 int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,

@@ -29,6 +29,8 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
                 unsigned long long* trace = nullptr);
 constexpr int CHOL_TRACE_SLOTS = 14;
 long long chol_task_count(const Geom& g);
+// ticket -> {proposal, tile row, tile column, kind}; returns the number of tickets
+long long chol_schedule_task(const Geom& g, long long ticket, int* out4);
 // solve_only: the top square already holds a lower-triangular factor; only the appended rows are
 // solved (X = B L^-T) -- the matrix-level forward / backward substitutions.
 size_t chol_smem_bytes();

@@ -23,6 +23,7 @@ EXPORTS = [
     "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
     "gpb_last_timing", "gpb_set_sched", "gpb_set_trace", "gpb_get_trace", "gpb_version",
     "gpb_plane_stats", "gpb_sample_plane", "gpb_draw", "gpb_mll_gradient",
+    "gpb_schedule_task",
 ]
 
 
@@ -98,6 +99,8 @@ def load():
                            _dp, _dp, _dp, _ip]
     L.gpb_mll_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(Term), C.c_int, _dp, C.c_int,
                                    C.c_double, C.c_int, _dp, _ip]
+    L.gpb_schedule_task.argtypes = [C.c_int, C.c_int, C.c_int, C.c_longlong, _ip]
+    L.gpb_schedule_task.restype = C.c_longlong
     L.gpb_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     L.gpb_set_sched.argtypes = [C.c_void_p, C.c_int]
     L.gpb_set_trace.argtypes = [C.c_void_p, C.c_int]
@@ -380,6 +383,20 @@ class Dataset:
             raise GpbError(st, f"proposal covariance not positive definite (info={info.value})")
         ctx._check(st)
         return states, ll, acc, info.value
+
+
+def schedule(n, appended=1, batch=1):
+    """Ticket order of the factorisation kernel: (tickets, 4) int array of {proposal, tile row, tile
+    column, kind} (gpb_schedule_task; host only)."""
+    L = load()
+    probe = (C.c_int * 4)()
+    total = int(L.gpb_schedule_task(n, appended, batch, -1, probe))
+    if total < 0:
+        raise GpbError(total, "gpb_schedule_task")
+    out = np.zeros((total, 4), dtype=np.int32)
+    for t in range(total):
+        L.gpb_schedule_task(n, appended, batch, t, out[t].ctypes.data_as(_ip))
+    return out
 
 
 def philox_streams(seed, chain0, chains, iters, P):

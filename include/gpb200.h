@@ -200,6 +200,14 @@ int gpb_set_sched(gpb_ctx *ctx, int mode);
  * and returns the number of tasks of that call. */
 int gpb_set_trace(gpb_ctx *ctx, int enable);
 long long gpb_get_trace(gpb_ctx *ctx, unsigned long long *out, long long max_tasks);
+/* Schedule introspection (host only, no device needed): the task that ticket `ticket` of the
+ * factorisation kernel stands for, in a system of n training rows + `appended` extra rows and `batch`
+ * proposals.  out4 = {proposal, tile row, tile column, kind}; kind 0 = plain tile (contract, solve),
+ * 1 = first diagonal block, 2 = pre-accumulation of diagonal block `tile row` over all but its last
+ * block column, 3 = fused: solve tile (j+1, j), then update and factor diagonal block j+1.  Returns the
+ * number of tickets (out4 untouched when the ticket is out of range), or a negative status.  Tickets
+ * are drawn in increasing order and every task only depends on lower tickets (tests/). */
+long long gpb_schedule_task(int n, int appended, int batch, long long ticket, int *out4);
 const char *gpb_version(void);
 
 #ifdef __cplusplus

@@ -186,3 +186,53 @@ def test_hmc_family_host_logic_on_a_toy_target():
             assert np.allclose(xs, xs[0])
     finally:
         gp.DualAverage.as_executed, gp.Ehmc.as_executed = old
+
+
+@pytest.mark.parametrize("n,appended,batch", [(1, 1, 1), (64, 1, 1), (65, 1, 3), (300, 1, 2), (300, 0, 1), (500, 130, 2),
+                                              (1024, 1, 5), (130, 200, 1)])
+def test_ticket_order_of_the_factorisation_kernel_is_topological(n, appended, batch):
+    """The persistent factorisation kernel draws tickets in increasing order and a CTA only ever waits for
+    results of lower tickets -- that is what makes its spin-waits deadlock-free.  Checked on the kernel's
+    own decoder (gpb_schedule_task runs the same decode_task on the host): every tile is produced exactly
+    once, and every input of every task is produced by a lower ticket."""
+    from gpb200 import _lib as G
+    PLAIN, DIAG0, PART, FUSED = 0, 1, 2, 3
+    sched = G.schedule(n, appended, batch)
+    nt = (n + 63) // 64
+    rt = nt + (appended + 63) // 64
+    assert len(sched) == batch * (nt * rt - nt * (nt - 1) // 2)
+    final, partial = {}, {}          # (b, i, j) -> ticket that makes the tile final / pre-accumulates it
+    for t, (b, i, j, kind) in enumerate(sched):
+        b, i, j, kind = int(b), int(i), int(j), int(kind)
+        assert 0 <= b < batch and 0 <= j < nt and j <= i < rt
+        if kind == DIAG0:
+            assert (i, j) == (0, 0)
+            assert final.setdefault((b, 0, 0), t) == t
+        elif kind == PART:
+            assert i == j and 1 <= j < nt
+            assert partial.setdefault((b, i, i), t) == t
+        elif kind == FUSED:
+            assert i == j + 1 and i < nt
+            assert final.setdefault((b, i, j), t) == t and final.setdefault((b, i, i), t) == t
+        else:
+            assert i > j and not (i == j + 1 and i < nt)
+            assert final.setdefault((b, i, j), t) == t
+    for b in range(batch):           # every tile of the lower trapezoid exactly once
+        for j in range(nt):
+            for i in range(j, rt):
+                assert (b, i, j) in final, (b, i, j)
+            if j >= 1:
+                assert (b, j, j) in partial
+    assert len(final) == batch * (nt * rt - nt * (nt - 1) // 2)
+    for t, (b, i, j, kind) in enumerate(sched):
+        b, i, j, kind = int(b), int(i), int(j), int(kind)
+        if kind == DIAG0:
+            continue
+        if kind == PART:             # block (i, i) over the block columns k < i - 1
+            deps = [(b, i, k) for k in range(i - 1)]
+        else:                        # tile (i, j): both row panels left of column j, and diag(j) for the solve
+            deps = [(b, i, k) for k in range(j)] + [(b, j, k) for k in range(j + 1)]
+        for d in deps:
+            assert final[d] < t, (t, (b, i, j, kind), d)
+        if kind == FUSED and i >= 2:  # the pre-accumulated block it finishes (block 1 has nothing to pre-accumulate)
+            assert partial[(b, i, i)] < t

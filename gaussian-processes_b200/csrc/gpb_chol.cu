@@ -954,14 +954,30 @@ long long chol_schedule_task(const Geom& g_in, long long ticket, int* out4) {
 
 int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,
                 SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace) {
-  cudaFuncSetAttribute(k_chol_tasks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
-  cudaFuncSetAttribute(k_chol_tasks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+  // per host thread (one gpb_ctx per thread): the attribute is set once per device, and the two TMA
+  // descriptors are re-encoded only when the workspace or the geometry changed -- both are pure host
+  // latency on every small call otherwise
+  struct Cache { int dev = -1; const double* mats = nullptr; const double* linvt = nullptr; int ld = 0, npad = 0, batch = 0;
+                 size_t stride = 0; CUtensorMap tmap, tmapL; };
+  thread_local Cache cc;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (cc.dev != dev) {
+    cudaFuncSetAttribute(k_chol_tasks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cudaFuncSetAttribute(k_chol_tasks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cc.dev = dev; cc.mats = nullptr;
+  }
   Geom g = g_in;
   if (mode != 0 || g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;  // debug mode: one group
-  CUtensorMap tmap;
-  if (!make_tmap(&tmap, g, mats)) return -1;
-  CUtensorMap tmapL;
-  if (!make_tmap_linvt(&tmapL, g, linvt)) return -1;
+  if (cc.mats != mats || cc.linvt != linvt || cc.ld != g.ld || cc.npad != g.npad || cc.batch != g.batch ||
+      cc.stride != g.mat_stride) {
+    cc.mats = nullptr;
+    if (!make_tmap(&cc.tmap, g, mats)) return -1;
+    if (!make_tmap_linvt(&cc.tmapL, g, linvt)) return -1;
+    cc.mats = mats; cc.linvt = linvt; cc.ld = g.ld; cc.npad = g.npad; cc.batch = g.batch; cc.stride = g.mat_stride;
+  }
+  const CUtensorMap& tmap = cc.tmap;
+  const CUtensorMap& tmapL = cc.tmapL;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
   int launches = 0;
   {

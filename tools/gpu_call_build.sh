@@ -1,4 +1,3 @@
 #!/bin/bash
 timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
 timeout 200 python tools/latency_probe.py 2>&1 | tail -8
-timeout 300 python tools/c3_breakdown.py 2>&1 | head -9

@@ -528,11 +528,20 @@ class KernelParameters:
             kp = KernelParameters.constrainParams(params.kernelParameters)
             return sum(pr.logPdf(pa) for pr, pa in zip(prior, p)) + llf(params.copy(kernelParameters=kp))
 
-        def grad(p):
-            params = KernelParameters.arrayToParams(init, p)
-            evalPrior = [pr.gradLogPdf(pa) for pr, pa in zip(prior, p)]
-            return np.array([a + b for a, b in zip(gradf(params), evalPrior)])
+        last = {}
 
+        def grad(p):
+            # Hmc.leapfrog asks for the gradient at the end of one step and again at the start of the next
+            # (Hmc.scala:30-39): the same point, and the device call is deterministic -- one-entry memo
+            key = np.asarray(p, dtype=np.float64).tobytes()
+            if last.get("key") != key:
+                params = KernelParameters.arrayToParams(init, p)
+                evalPrior = [pr.gradLogPdf(pa) for pr, pa in zip(prior, p)]
+                last["key"], last["val"] = key, np.array([a + b for a, b in zip(gradf(params), evalPrior)])
+                last["calls"] = last.get("calls", 0) + 1
+            return last["val"].copy()
+
+        grad.stats = last
         kp = KernelParameters.unconstrainParams(init.kernelParameters)
         return ll, grad, KernelParameters.paramsToArray(init.copy(kernelParameters=kp))
 

@@ -19,6 +19,7 @@ pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "gp_golden.json")
 SE_W = [("se", 3.0, 5.5), ("white", 0.5)]
 SE_SE_W = [("se", 3.0, 5.5), ("se", 1.0, 0.8), ("white", 0.5)]
+SHORT_W = [("se", 3.0, 0.2), ("white", 0.5)]
 LL_RTOL = 1e-10
 
 
@@ -60,7 +61,10 @@ def test_build_cov_and_distance_entrywise(ctx, oracle, n, dim):
 @pytest.mark.parametrize("sched", [0, 1])
 @pytest.mark.parametrize("n,dim,terms", [
     (1, 1, SE_W), (2, 1, SE_W), (3, 2, SE_SE_W), (20, 1, SE_W), (63, 2, SE_W), (64, 1, SE_SE_W),
-    (65, 2, SE_W), (300, 1, SE_W), (300, 2, SE_SE_W), (1024, 2, SE_W)])
+    (65, 2, SE_W), (300, 1, SE_W), (300, 2, SE_SE_W), (1024, 2, SE_W),
+    # length scale 0.2 on [-10, 10]: -d^2/s^2 reaches -20000, most SE entries underflow -- the rare
+    # branch of the hot-path exp (arguments below -700 go to the library routine)
+    (128, 2, SHORT_W), (192, 1, SHORT_W), (256, 2, [("white", 0.5), ("se", 3.0, 0.2), ("se", 1.0, 5.0)])])
 def test_loglik_parity(ctx, oracle, sched, n, dim, terms):
     ctx.set_sched(sched)
     try:

@@ -1,6 +1,8 @@
 // gpb_api.cu -- the C ABI of libgpb200.so (include/gpb200.h): contexts, datasets, workspace and
 // the host-side sequencing of the sm_100a kernels.  No CPU fallback anywhere: every entry point
 // either runs the CUDA path or returns an error status.
+#include <cstdlib>
+
 #include "gpb_host.h"
 
 using namespace gpb;
@@ -27,6 +29,11 @@ Geom make_geom(int n, int dim, int m, bool with_rhs, int batch, int design, bool
   g.batch = batch;
   g.tgroup = batch;
   g.ident0 = identity ? g.nt : -1;
+  const int arows = m + design + (with_rhs ? 1 : 0);   // appended rows in use
+  g.light_row = (arows > 0 && arows - (g.apad - TILE) <= 8) ? g.rt - 1 : -1;
+  // GPB_LIGHT_ROWS=0: run that tile row like every other one (the results must not change: tests)
+  static const bool light_on = [] { const char* e = getenv("GPB_LIGHT_ROWS"); return !(e && e[0] == '0'); }();
+  if (!light_on) g.light_row = -1;
   g.mat_stride = (size_t)g.ld * g.npad;
   return g;
 }

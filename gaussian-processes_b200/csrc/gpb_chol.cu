@@ -583,6 +583,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     const int kind = solve_only ? K_PLAIN : d.kind;
     if (k0 < 0 || (kind == K_PART && d.j == 1)) continue;
     const int kend = (kind == K_PART) ? d.j - 1 : d.j;
+    // Tile row with at most 8 rows in use (the rhs row of the likelihood): one 8-row DMMA fragment per
+    // 8 tile columns instead of the whole 64-row tile -- the same operations on the live entries, in
+    // the same order, so the results do not change; the dead rows are zero and stay untouched.
+    const bool light = (d.i == g.light_row);
     double* M = mats + (size_t)d.b * g.mat_stride;
     int* done_b = done + (size_t)d.b * g.rt;
     int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
@@ -652,7 +656,78 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
 #pragma unroll
       for (int nt = 0; nt < NTW; ++nt) bb[nt] = P[(KC + k) * LDT + wr * RW + nt * 8 + gq];
     };
-    if (nstage > 0) {
+    if (light) {
+      // the tile goes to Cs as it is (dead rows: zeros); the live fragment (rows 0..7, warps wr == 0)
+      // stays in registers and is written over it after the contraction
+      double la[4][2];
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+        la[mt][0] = acc[mt][0][0]; la[mt][1] = acc[mt][0][1];
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) {
+          const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+          *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+        }
+      }
+      __syncwarp();                      // the stores consumed the tile: its LDS are done
+      release_pre();
+      auto light_frag = [&](const double* P, double (&a)[KC / 4][4], double (&b)[KC / 4]) {
+#pragma unroll
+        for (int ks = 0; ks < KC / 4; ++ks) {
+          const int k = ks * 4 + tq;
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt) a[ks][mt] = -P[k * LDT + wc * 32 + mt * 8 + gq];
+          b[ks] = P[(KC + k) * LDT + gq];
+        }
+      };
+      if (nstage > 0 && wr == 0) {
+        wait_full(stage, phase);
+        double a[KC / 4][4], b[KC / 4];
+        light_frag(&sm.stage[stage][0], a, b);
+#pragma unroll 1
+        for (int it = 0; it < nstage; ++it) {
+          uint32_t nst = stage + 1, nph = phase;
+          if (nst == STAGES) { nst = 0; nph ^= 1; }
+          double an[KC / 4][4], bn[KC / 4];
+          if (it + 1 < nstage) {
+            wait_full(nst, nph);
+            light_frag(&sm.stage[nst][0], an, bn);
+          } else {
+#pragma unroll
+            for (int ks = 0; ks < KC / 4; ++ks) {
+              bn[ks] = 0.0;
+#pragma unroll
+              for (int mt = 0; mt < 4; ++mt) an[ks][mt] = 0.0;
+            }
+          }
+#pragma unroll
+          for (int ks = 0; ks < KC / 4; ++ks)
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) dmma884(la[mt][0], la[mt][1], a[ks][mt], b[ks]);
+#pragma unroll
+          for (int ks = 0; ks < KC / 4; ++ks) {
+            b[ks] = bn[ks];
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) a[ks][mt] = an[ks][mt];
+          }
+          // this stage's fragments were fetched one iteration ago and its DMMAs have issued
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.empty[stage]);
+          stage = nst; phase = nph;
+        }
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+          *reinterpret_cast<double2*>(&sm.Cs[(wc * 32 + mt * 8 + gq) * LDT + 2 * tq]) = make_double2(la[mt][0], la[mt][1]);
+      } else {
+        // the warps of the dead rows only keep the ring turning
+#pragma unroll 1
+        for (int it = 0; it < nstage; ++it) {
+          wait_full(stage, phase);
+          if (lane == 0) mbar_arrive(&sm.empty[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if (nstage > 0) {
       wait_full(stage, phase);
       double a[4], bb[NTW];
       load_frag(&sm.stage[stage][0], 0, a, bb);
@@ -713,13 +788,15 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       continue;
     }
     // acc -> Cs (column-major [c][r])
+    if (!light) {
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
+      for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-      for (int nt = 0; nt < NTW; ++nt) {
-        const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
-        *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
-      }
+        for (int nt = 0; nt < NTW; ++nt) {
+          const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+          *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+        }
+    }
     if (tid == 0) sm.bad_col = -1;
     bar_named(1, NCONS);
     release_pre();
@@ -769,6 +846,29 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       constexpr int CTW = CT / (CW / 4);     // ... per warp
       const int rq = warp & 3, ch = warp >> 2;
       double xs[LT_STAGES][CTW][2][2];       // X stays in registers: K_FUSED needs it again (s loop unrolled)
+      if (light) {
+        // rows 0..7 only: warp w solves the w-th 8-column tile of each stage (same k order as below)
+#pragma unroll 1
+        for (int s = 0; s < LT_STAGES; ++s) {
+          wait_full(stage, phase);
+          if (tr && s == 0) tr[4] = clock64();
+          if (warp < CT) {
+            const double* LTs = &sm.stage[stage][warp * 8 * LDT];
+            double x0 = 0.0, x1 = 0.0;
+            const int kmax = s * SCOLS + (warp + 1) * 8;
+#pragma unroll 4
+            for (int kb = 0; kb < kmax; kb += 4) {
+              const int k = kb + tq;
+              dmma884(x0, x1, LTs[gq * LDT + k], sm.Cs[k * LDT + gq]);
+            }
+            const int c = s * SCOLS + warp * 8 + gq;
+            *reinterpret_cast<double2*>(Aij + (size_t)c * g.ld + 2 * tq) = make_double2(x0, x1);
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.empty[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      } else
 #pragma unroll
       for (int s = 0; s < LT_STAGES; ++s) {
         wait_full(stage, phase);

@@ -37,6 +37,8 @@ struct Geom {
   int batch;
   int tgroup;           // proposals per ticket group of the factorisation kernel (<= batch)
   int ident0;           // first tile row of an appended identity block (npad rows -> L^-T), or -1
+  int light_row;        // last tile row when at most 8 of its rows are in use (the rhs row, design rows), or -1:
+                        // its tasks run one 8-row DMMA fragment instead of the 64-row tile (k_chol_tasks)
   size_t mat_stride;    // doubles between consecutive matrices
 };
 

@@ -571,3 +571,44 @@ def test_ehmc_device_driven_matches_oracle_driven(oracle):
         gp.GaussianProcess.formula, gp.GaussianProcess.gradient_mode, gp.DualAverage.as_executed, gp.Ehmc.as_executed = old
     assert np.all(np.isfinite(dev))
     assert np.allclose(dev, ref, rtol=1e-6, atol=1e-8)
+
+
+_LIGHT_SCRIPT = r"""
+import json, sys, os
+import numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "gaussian-processes_b200"))
+from gpb200 import _lib as G
+ctx = G.Context(0)
+out = []
+for n, dim, B, m in [(300, 1, 3, 0), (1024, 2, 5, 0), (150, 2, 1, 69), (64, 1, 1, 8)]:
+    rng = np.random.default_rng(1000 + n)
+    x = rng.uniform(-10, 10, size=(n, dim)); y = rng.standard_normal(n)
+    ds = ctx.dataset(x, y)
+    props = [[(0, 3.0 + 0.1 * b, 5.5), (1, 0.5, 0.0)] for b in range(B)]
+    rs = ds.loglik_batch(props, nugget=1e-3)
+    rec = [[float(r.Q).hex(), float(r.U1).hex(), float(r.S).hex(), r.info] for r in rs]
+    if m:
+        mean, var, info = ds.predict(props[0], rng.uniform(-10, 10, size=(m, dim)), nugget=1e-3)
+        rec.append([float(v).hex() for v in mean] + [float(v).hex() for v in var] + [info])
+    out.append(rec)
+    ds.close()
+print("RESULT" + json.dumps(out))
+"""
+
+
+def test_light_rhs_row_tasks_change_nothing():
+    """The tile row that only holds the rhs row (<= 8 rows in use) is contracted and solved as one
+    8-row DMMA fragment (Geom.light_row, gpb_chol.cu).  Same operations in the same order on the live
+    entries: every output is bit-identical to the full-tile path (GPB_LIGHT_ROWS=0)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for light in ("1", "0"):
+        env = dict(os.environ, GPB_LIGHT_ROWS=light)
+        p = subprocess.run([sys.executable, "-c", _LIGHT_SCRIPT, root], env=env, capture_output=True, text=True, timeout=600)
+        assert p.returncode == 0, p.stderr[-2000:]
+        line = [l for l in p.stdout.splitlines() if l.startswith("RESULT")][-1]
+        outs.append(json.loads(line[len("RESULT"):]))
+    assert outs[0] == outs[1]
+    assert all(rec[0][3] == 0 for rec in outs[0])

@@ -79,4 +79,5 @@ def main():
             if j + 1 >= nt: continue
             a = tr[d[(j + 1, j)]]; b = tr[d[(j + 1, j + 1)]]; dj = tr[d[(j, j)]]
             print(f"  col {j}: diag({j}) rel {(dj[7]-g0)/1e3:.1f} | A recv {(a[0]-g0)/1e3:.1f} rel {(a[7]-g0)/1e3:.1f} (dep->done {us(a[5]-a[4]):.1f}, done->rel {us(a[6]-a[5]):.1f}) | diag({j+1}) recv {(b[0]-g0)/1e3:.1f} factor {us(b[5]-b[4]):.1f} rel {(b[7]-g0)/1e3:.1f}")
-main()
+if __name__ == "__main__":
+    main()

@@ -394,8 +394,11 @@ __device__ __forceinline__ int wait_counter_serving(const int* ctr, int need, in
 
 // TRACE = true is the schedule-analysis build of the same kernel (gpb_set_trace); the production
 // instantiation carries no timestamp code or registers.
-template <bool TRACE>
-__global__ void __launch_bounds__(NTHREADS, GPB_MINBLOCKS)
+// MINB = CTAs per SM the register budget is sized for: 2 (168 registers) for throughput launches, 1
+// (no register cap, no spills in the factor / solve phases) for launches bound by the dependency
+// chain, which run one CTA per SM anyway (n=4096, one proposal: 1.53 -> 1.38 ms).
+template <bool TRACE, int MINB>
+__global__ void __launch_bounds__(NTHREADS, MINB)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapL, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
              int static_sched, int solve_only, unsigned long long* __restrict__ trace) {
@@ -1063,8 +1066,9 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   int dev = 0;
   cudaGetDevice(&dev);
   if (cc.dev != dev) {
-    cudaFuncSetAttribute(k_chol_tasks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
-    cudaFuncSetAttribute(k_chol_tasks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cudaFuncSetAttribute(k_chol_tasks<false, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cudaFuncSetAttribute(k_chol_tasks<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cudaFuncSetAttribute(k_chol_tasks<true, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cc.dev = dev; cc.mats = nullptr;
   }
   Geom g = g_in;
@@ -1087,33 +1091,34 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     ++launches;
   }
   if (mode == 0) {
-    // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; single small proposals
-    // are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA that
-    // has its SM to itself factors and solves about twice as fast (n=4096, one proposal: 1.66 ms
-    // vs 2.14 ms).  GPB_CTAS_PER_SM_RT overrides (tuning).
+    // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; launches with few tasks
+    // per SM are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA
+    // that has its SM (and an uncapped register budget) to itself factors and solves faster (n=4096,
+    // one proposal: 1.36 ms vs 1.94 ms).  Measured crossover (tools/ctas_sweep.py, n = 300 .. 8192):
+    // about 24 tasks per SM.  GPB_CTAS_PER_SM_RT overrides (tuning).
     static int env_ctas = -1;
     if (env_ctas < 0) { const char* e = getenv("GPB_CTAS_PER_SM_RT"); env_ctas = e ? atoi(e) : 0; }
-    // work-bound (contraction time at ~28 TFLOP/s) vs chain-bound (~25 us per block column)
-    const double work_us = (double)g.batch * g.npad * (double)g.npad * g.ld / 3.0 / 28e6;
-    const double chain_us = 25.0 * g.nt;
-    int ctas = (work_us >= chain_us) ? CTAS_PER_SM : 1;
+    int ctas = (total >= 24LL * num_sms) ? CTAS_PER_SM : 1;
     if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
     const long long slots = (long long)num_sms * ctas;
     int grid = (int)(total < slots ? total : slots);
     if (trace)
-      k_chol_tasks<true><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                                   (int)total, 0, solve_only, trace);
+      k_chol_tasks<true, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                                  (int)total, 0, solve_only, trace);
+    else if (ctas == 1)
+      k_chol_tasks<false, 1><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                       (int)total, 0, solve_only, trace);
     else
-      k_chol_tasks<false><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                                    (int)total, 0, solve_only, trace);
+      k_chol_tasks<false, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                                   (int)total, 0, solve_only, trace);
     ++launches;
   } else {
     // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
     auto run = [&](long long begin, long long count) {
       if (count <= 0) return;
       int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
-      k_chol_tasks<false><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
-                                                                    (int)begin, (int)(begin + count), 1, solve_only, nullptr);
+      k_chol_tasks<false, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
+                                                                                   (int)begin, (int)(begin + count), 1, solve_only, nullptr);
       ++launches;
     };
     run(0, g.batch);

@@ -205,6 +205,11 @@ __device__ __forceinline__ double fast_rsqrt(double a) {
   return fma(0.5 * y, e, y);
 }
 
+// Sign flip on the integer pipe (the FP64 pipe is the one the DMMAs need).
+__device__ __forceinline__ double flip_sign(double x) {
+  return __hiloint2double(__double2hiint(x) ^ (int)0x80000000, __double2loint(x));
+}
+
 // Factor the stacked 128x64 [C; I]: top rows (sm.Cs) end as L_jj, bottom rows W (starts as the
 // identity) as L_jj^-T -- the inverse costs no extra dependent step.  W lives in LT_STAGES ring
 // stages the producer grants to the diagonal task (stage s0 + c / SCOLS holds columns c of W, pitch
@@ -652,10 +657,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     // refill (async proxy) was observed to overtake them.  Releasing stage s only while stage s+1
     // is being consumed guarantees every DMMA that read s has issued, i.e. its LDS completed.
     int pend = -1;
+    // The contraction runs on the NEGATED accumulator, acc' = -A + sum L L^T, so that the fragments
+    // enter the DMMAs as loaded: negating them at the stage boundary put four DADDs that wait on the
+    // LDS in front of the next 16 DMMAs.  Rounding is sign-symmetric, so -acc' is bit for bit the
+    // A - sum L L^T of the direct form (only the sign of an exact zero can differ).
     auto load_frag = [&](const double* P, int ks, double (&a)[4], double (&bb)[NTW]) {
       const int k = ks * 4 + tq;
 #pragma unroll
-      for (int mt = 0; mt < 4; ++mt) a[mt] = -P[k * LDT + wc * 32 + mt * 8 + gq];
+      for (int mt = 0; mt < 4; ++mt) a[mt] = P[k * LDT + wc * 32 + mt * 8 + gq];
 #pragma unroll
       for (int nt = 0; nt < NTW; ++nt) bb[nt] = P[(KC + k) * LDT + wr * RW + nt * 8 + gq];
     };
@@ -731,6 +740,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         }
       }
     } else if (nstage > 0) {
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) { acc[mt][nt][0] = flip_sign(acc[mt][nt][0]); acc[mt][nt][1] = flip_sign(acc[mt][nt][1]); }
       wait_full(stage, phase);
       double a[4], bb[NTW];
       load_frag(&sm.stage[stage][0], 0, a, bb);
@@ -739,15 +752,18 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         const double* P = &sm.stage[stage][0];
         uint32_t nst = stage + 1, nph = phase;
         if (nst == STAGES) { nst = 0; nph ^= 1; }
+        bool next_ready = true;
 #pragma unroll
         for (int ks = 0; ks < KC / 4; ++ks) {
           // fragments of the next k-step (or of the next stage's first k-step) are fetched before
           // this step's 16 DMMAs issue, so neither the LDS latency nor the barrier probe is exposed
           double an[4], bn[NTW];
+          // the barrier of the next stage is probed one k-step before its result is needed
+          if (ks == KC / 4 - 2) next_ready = (it + 1 >= nstage) || mbar_test_wait(&sm.full[nst], nph);
           if (ks + 1 < KC / 4) {
             load_frag(P, ks + 1, an, bn);
           } else if (it + 1 < nstage) {
-            wait_full(nst, nph);
+            if (!next_ready) wait_full(nst, nph);
             load_frag(&sm.stage[nst][0], 0, an, bn);
           } else {
 #pragma unroll
@@ -770,6 +786,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         pend = (int)stage;
         stage = nst; phase = nph;
       }
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NTW; ++nt) { acc[mt][nt][0] = flip_sign(acc[mt][nt][0]); acc[mt][nt][1] = flip_sign(acc[mt][nt][1]); }
     }
 
     if (tr) { tr[3] = clock64(); tr[8] = (unsigned long long)not_ready; tr[9] = 0; }

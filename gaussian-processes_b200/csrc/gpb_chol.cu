@@ -459,7 +459,9 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         if (lane == 0) t_next = fetch();
         continue;
       }
-      if (!solve_only) posted += (kind == K_FUSED) ? 2 : 1;
+      // (the chain-bound instantiation publishes diagonal blocks itself, see factor_block)
+      if (!solve_only) posted += (MINB == 1) ? ((kind == K_FUSED || kind == K_PART || (kind == K_PLAIN && d.i != d.j)) ? 1 : 0)
+                                             : ((kind == K_FUSED) ? 2 : 1);
       const int kend = (kind == K_PART) ? d.j - 1 : d.j;   // K_PART leaves the last block column to K_FUSED
       const int* done_b = done + (size_t)d.b * g.rt;
       const int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
@@ -837,7 +839,13 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       diag_factor(sm, s0, Ajj, LTj, g.ld, tid);
       bar_named(1, NCONS);             // bad_col is final; every read of the scratch stages is done
       if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, dj * TILE + sm.bad_col + 1);  // 1-based pivot
-      post_release(done_b + dj, dj + 1);
+      if (MINB == 1) {
+        // chain-bound launches: the next block column waits for exactly this store, so thread 0
+        // publishes it right here instead of handing it to the (possibly sleeping) producer lane
+        if (tid == 0) { __threadfence(); fence_proxy_async(); st_release(done_b + dj, dj + 1); }
+      } else {
+        post_release(done_b + dj, dj + 1);
+      }
       fence_proxy_async();             // generic writes to the scratch stages before TMA refills them
       __syncwarp();
       if (lane == 0)

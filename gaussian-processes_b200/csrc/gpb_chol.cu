@@ -913,7 +913,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
         const int kmax = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
         const int kfull = kmax - (CTW - 1) * 8;   // below this every column tile of the warp is live
-#pragma unroll 2
+#pragma unroll (MINB == 1 ? 4 : 2)
         for (int kb = 0; kb < kfull; kb += 4) {
           const int k = kb + tq;
           double a[CTW], bb[2];
@@ -984,41 +984,102 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         pre1 = (int)stage;
         wait_full(stage, phase);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        {
-          const double* T = &sm.stage[wc == 0 ? pre0 : pre1][0];
+        if constexpr (MINB == 1 && CW == 4) {
+          // Chain-bound instantiation: this update sits on the dependency chain, and it is a SYRK --
+          // only fragments on or below the diagonal of the block are ever read (diag_factor works on
+          // rows >= columns; what Cs holds above the diagonal never reaches a result).  Warp 2, whose
+          // sub-tile lies strictly above the diagonal, takes tile columns 16..31 of warp 1's full
+          // sub-tile (8 fragments each); warps 0 and 3 run the 10 lower fragments of theirs: 10/16
+          // of the time, the same operations per entry in the same order.
+          const bool halfw = (warp == 1 || warp == 2);
+          const int wcE = (warp == 2) ? 0 : wc, wrE = (warp == 2) ? 1 : wr, cofs = (warp == 2) ? 16 : 0;
+          const double* T = &sm.stage[wcE == 0 ? pre0 : pre1][0];
 #pragma unroll
           for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
             for (int nt = 0; nt < NTW; ++nt) {
-              const double2 v = *reinterpret_cast<const double2*>(&T[(mt * 8 + gq) * LDT + wr * RW + nt * 8 + 2 * tq]);
+              if (halfw ? mt >= 2 : nt < mt) continue;
+              const double2 v = *reinterpret_cast<const double2*>(&T[(cofs + mt * 8 + gq) * LDT + wrE * RW + nt * 8 + 2 * tq]);
               acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
             }
-        }
-        bar_named(1, NCONS);             // X is complete in Cs
-        // same k order as the streamed chunk it replaces (16 k-steps of 4): bitwise the same block
+          bar_named(1, NCONS);             // X is complete in Cs
+          if (halfw) {
 #pragma unroll 4
-        for (int ks = 0; ks < TILE / 4; ++ks) {
-          const int k = ks * 4 + tq;
-          double a[4], bb[NTW];
+            for (int ks = 0; ks < TILE / 4; ++ks) {
+              const int k = ks * 4 + tq;
+              double a[2], bb[NTW];
 #pragma unroll
-          for (int mt = 0; mt < 4; ++mt) a[mt] = -sm.Cs[k * LDT + wc * 32 + mt * 8 + gq];
+              for (int mt = 0; mt < 2; ++mt) a[mt] = -sm.Cs[k * LDT + cofs + mt * 8 + gq];
 #pragma unroll
-          for (int nt = 0; nt < NTW; ++nt) bb[nt] = sm.Cs[k * LDT + wr * RW + nt * 8 + gq];
+              for (int nt = 0; nt < NTW; ++nt) bb[nt] = sm.Cs[k * LDT + RW + nt * 8 + gq];
+#pragma unroll
+              for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+            }
+          } else {
+#pragma unroll 4
+            for (int ks = 0; ks < TILE / 4; ++ks) {
+              const int k = ks * 4 + tq;
+              double a[4], bb[NTW];
+#pragma unroll
+              for (int mt = 0; mt < 4; ++mt) a[mt] = -sm.Cs[k * LDT + wc * 32 + mt * 8 + gq];
+#pragma unroll
+              for (int nt = 0; nt < NTW; ++nt) bb[nt] = sm.Cs[k * LDT + wr * RW + nt * 8 + gq];
+#pragma unroll
+              for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                for (int nt = mt; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+            }
+          }
+          __syncwarp();
+          release_pre();
+          bar_named(1, NCONS);             // every warp has read X: Cs may take the block
 #pragma unroll
           for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-            for (int nt = 0; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
-        }
-        __syncwarp();
-        release_pre();
-        bar_named(1, NCONS);             // every warp has read X: Cs may take the block
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-          for (int nt = 0; nt < NTW; ++nt) {
-            const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
-            *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+            for (int nt = 0; nt < NTW; ++nt) {
+              if (halfw ? mt >= 2 : nt < mt) continue;
+              const int c = wcE * 32 + cofs + mt * 8 + gq, r = wrE * RW + nt * 8 + 2 * tq;
+              *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+            }
+        } else {
+        {
+            const double* T = &sm.stage[wc == 0 ? pre0 : pre1][0];
+  #pragma unroll
+            for (int mt = 0; mt < 4; ++mt)
+  #pragma unroll
+              for (int nt = 0; nt < NTW; ++nt) {
+                const double2 v = *reinterpret_cast<const double2*>(&T[(mt * 8 + gq) * LDT + wr * RW + nt * 8 + 2 * tq]);
+                acc[mt][nt][0] = v.x; acc[mt][nt][1] = v.y;
+              }
           }
+          bar_named(1, NCONS);             // X is complete in Cs
+          // same k order as the streamed chunk it replaces (16 k-steps of 4): bitwise the same block
+  #pragma unroll 4
+          for (int ks = 0; ks < TILE / 4; ++ks) {
+            const int k = ks * 4 + tq;
+            double a[4], bb[NTW];
+  #pragma unroll
+            for (int mt = 0; mt < 4; ++mt) a[mt] = -sm.Cs[k * LDT + wc * 32 + mt * 8 + gq];
+  #pragma unroll
+            for (int nt = 0; nt < NTW; ++nt) bb[nt] = sm.Cs[k * LDT + wr * RW + nt * 8 + gq];
+  #pragma unroll
+            for (int mt = 0; mt < 4; ++mt)
+  #pragma unroll
+              for (int nt = 0; nt < NTW; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+          }
+          __syncwarp();
+          release_pre();
+          bar_named(1, NCONS);             // every warp has read X: Cs may take the block
+  #pragma unroll
+          for (int mt = 0; mt < 4; ++mt)
+  #pragma unroll
+            for (int nt = 0; nt < NTW; ++nt) {
+              const int c = wc * 32 + mt * 8 + gq, r = wr * RW + nt * 8 + 2 * tq;
+              *reinterpret_cast<double2*>(&sm.Cs[c * LDT + r]) = make_double2(acc[mt][nt][0], acc[mt][nt][1]);
+            }
+        }
         if (tid == 0) sm.bad_col = -1;
         bar_named(1, NCONS);
         factor_block(d.i, M + (size_t)(d.i * TILE) * g.ld + (size_t)d.i * TILE,

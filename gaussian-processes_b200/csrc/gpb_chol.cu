@@ -76,7 +76,9 @@ struct __align__(128) CholSmem {
 };
 
 size_t chol_smem_bytes() { return sizeof(CholSmem); }
-size_t chol_linvt_doubles(const Geom& g) { return (size_t)g.batch * g.nt * TILE * LDT; }
+// [batch][nt] tiles L_jj^-T, followed by ONE identity tile (same pitch): the start value of the
+// stacked inverse rows, TMA-loaded into the scratch stages of every diagonal factorisation
+size_t chol_linvt_doubles(const Geom& g) { return ((size_t)g.batch * g.nt + 1) * TILE * LDT; }
 long long chol_task_count(const Geom& g) {
   return (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
 }
@@ -158,9 +160,14 @@ __device__ __forceinline__ int task_k0(const Geom& g, const TaskDesc& d) {
 // One launch instead of three memsets (+ a preset): zero the progress counters and flags, info and the
 // ticket counter (`error` stays sticky until the host has read it); preset done[i] = I for the rows of
 // an appended identity block.
-__global__ void k_chol_reset(Geom g, int* __restrict__ done, int* __restrict__ info, SchedState* sched) {
+__global__ void k_chol_reset(Geom g, int* __restrict__ done, int* __restrict__ info, SchedState* sched,
+                             double* __restrict__ linvt) {
   const int per = g.rt + g.nt;               // done [batch][rt] followed by part [batch][nt]
   const long long total = (long long)g.batch * per;
+  // the identity tile behind the L_jj^-T tiles (the workspace may have moved since the last launch)
+  double* ident = linvt + (size_t)g.batch * g.nt * TILE * LDT;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < TILE * LDT; e += gridDim.x * blockDim.x)
+    ident[e] = (e / LDT == e % LDT) ? 1.0 : 0.0;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     int v = 0;
     if (g.ident0 >= 0 && i < (long long)g.batch * g.rt) {
@@ -226,16 +233,21 @@ __device__ __forceinline__ double* wcol(CholSmem& sm, int s0, int c) {
   const unsigned uc = (unsigned)c;
   return &sm.stage[((unsigned)s0 + uc / SCOLS) % STAGES][(uc % SCOLS) * LDT];
 }
+// store_L = false leaves the L_jj tile in sm.Cs for write_L_tile: no task reads a diagonal tile of L
+// (the solves use L_jj^-T), so the chain-bound instantiation publishes L_jj^-T first and writes L_jj
+// behind the publication.
+__device__ __forceinline__ void write_L_tile(const CholSmem& sm, double* __restrict__ Aij, int ld, int tid) {
+  const int r = tid & (TILE - 1), half = tid >> 6;
+#pragma unroll 4
+  for (int c = half; c < TILE; c += NCONS / TILE)
+    if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
+}
 __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restrict__ Aij,
-                                         double* __restrict__ LT, int ld, int tid) {
+                                         double* __restrict__ LT, int ld, int tid, bool store_L) {
   const int warp = tid >> 5, lane = tid & 31, gq = lane >> 2, tq = lane & 3;
-  for (int e = tid; e < TILE * TILE; e += NCONS) {
-    const int c = e >> 6, k = e & (TILE - 1);
-    wcol(sm, s0, c)[k] = (c == k) ? 1.0 : 0.0;
-  }
+  // W arrives as the identity (TMA, producer warp); every thread has waited on those stages
   const bool top = tid < TILE, act = tid < 2 * TILE;   // threads beyond the 128 stacked rows only keep the barriers
   const int rr = top ? tid : (tid - TILE) & (TILE - 1);  // entry (R, c): top Cs[c * LDT + rr], bottom wcol(c)[rr]
-  bar_named(1, NCONS);
 #pragma unroll 1
   for (int c0 = 0; c0 < TILE; c0 += PB) {
     double p[PB];
@@ -328,7 +340,7 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
     const int r = tid & (TILE - 1), half = tid >> 6;
 #pragma unroll 4
     for (int c = half; c < TILE; c += NCONS / TILE) {
-      if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
+      if (store_L && r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
       LT[c * LDT + r] = (c >= r) ? wcol(sm, s0, c)[r] : 0.0;
     }
   }
@@ -468,6 +480,19 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       const int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
       unsigned long long* ptr_ = (TRACE && trace != nullptr && lane == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
       if (ptr_) ptr_[10] = clock64();
+      // scratch stages of a diagonal factorisation: they start as the identity (the stacked [C; I]),
+      // fetched by TMA from the identity tile behind linvt while the consumers are still updating C
+      auto load_identity = [&]() {
+        const int row0 = g.batch * g.nt * TILE;
+#pragma unroll 1
+        for (int s = 0; s < LT_STAGES; ++s) {
+          if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
+          mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
+          tma_load_2d(&sm.stage[stage][0], &tmapL, 0, row0 + s * SCOLS, &sm.full[stage]);
+          tma_load_2d(&sm.stage[stage][KC * LDT], &tmapL, 0, row0 + s * SCOLS + KC, &sm.full[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      };
       if (lane == 0) {
         // the tile itself (accumulator start value) comes first, as AT_STAGES ordinary stages:
         // stage s holds tile columns s*SCOLS .. in [column][LDT] order
@@ -533,21 +558,11 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
               tma_load_3d(&sm.stage[stage][KC * LDT], &tmap, d.i * TILE, col + KC, d.b, &sm.full[stage]);
               if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
-#pragma unroll 1
-            for (int s = 0; s < LT_STAGES; ++s) {
-              if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
-              mbar_arrive(&sm.full[stage]);
-              if (++stage == STAGES) { stage = 0; phase ^= 1; }
-            }
+            load_identity();
           }
         } else if (!solve_only) {
-          // diagonal task: grant LT_STAGES empty stages as scratch for the stacked inverse rows
-#pragma unroll 1
-          for (int s = 0; s < LT_STAGES; ++s) {
-            if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
-            mbar_arrive(&sm.full[stage]);
-            if (++stage == STAGES) { stage = 0; phase ^= 1; }
-          }
+          // diagonal task: LT_STAGES stages as scratch for the stacked inverse rows
+          load_identity();
         }
         if (ptr_) ptr_[13] = clock64();
       }
@@ -837,13 +852,15 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         wait_full(stage, phase);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      diag_factor(sm, s0, Ajj, LTj, g.ld, tid);
+      diag_factor(sm, s0, Ajj, LTj, g.ld, tid, !DIRECT_DIAG);
       bar_named(1, NCONS);             // bad_col is final; every read of the scratch stages is done
       if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, dj * TILE + sm.bad_col + 1);  // 1-based pivot
       if (DIRECT_DIAG) {
         // chain-bound launches: the next block column waits for exactly this store, so thread 0
-        // publishes it right here instead of handing it to the (possibly sleeping) producer lane
+        // publishes it right here instead of handing it to the (possibly sleeping) producer lane;
+        // L_jj itself (an output only) goes out behind the publication
         if (tid == 0) { __threadfence(); fence_proxy_async(); st_release(done_b + dj, dj + 1); }
+        write_L_tile(sm, Ajj, g.ld, tid);
       } else {
         post_release(done_b + dj, dj + 1);
       }
@@ -1111,7 +1128,7 @@ static EncodeFn tmap_encoder() {
 static bool make_tmap_linvt(CUtensorMap* tm, const Geom& g, double* linvt) {
   EncodeFn encode = tmap_encoder();
   if (!encode) return false;
-  const cuuint64_t dims[2] = {(cuuint64_t)LDT, (cuuint64_t)g.batch * g.nt * TILE};
+  const cuuint64_t dims[2] = {(cuuint64_t)LDT, ((cuuint64_t)g.batch * g.nt + 1) * TILE};   // + the identity tile
   const cuuint64_t strides[1] = {(cuuint64_t)LDT * sizeof(double)};
   const cuuint32_t box[2] = {(cuuint32_t)LDT, (cuuint32_t)KC};
   const cuuint32_t estr[2] = {1u, 1u};
@@ -1177,7 +1194,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   {
     const long long total = (long long)g.batch * (g.rt + g.nt);
     const int blocks = (int)((total + 255) / 256 < 296 ? (total + 255) / 256 : 296);
-    k_chol_reset<<<blocks, 256, 0, st>>>(g, done, info, sched);
+    k_chol_reset<<<blocks, 256, 0, st>>>(g, done, info, sched, linvt);
     ++launches;
   }
   if (mode == 0) {

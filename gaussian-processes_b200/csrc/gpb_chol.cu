@@ -442,10 +442,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     int q = 0, static_next = task_begin + blockIdx.x;
     RelState rs; rs.r = 0;
     int posted = 0;   // tasks handed to the consumers that will post a publication
-    // the next ticket is drawn while the current task's last stages are still in flight (after its
-    // contraction stages are issued, before its solve stages), so the atomic's latency is hidden.
-    // Drawing it earlier (at the start of the task) was measured and is worse for chain-bound launches:
-    // a busy CTA then holds a critical-path task in its own queue (n=1024 batch 32: 0.64 -> 0.72 ms).
+    // The next ticket is drawn when every load of the current task has been issued (its last stages
+    // are still in flight then, so the atomic's latency stays hidden).  The later, the better for
+    // launches that are partly bound by the dependency chain: a busy CTA that draws early sits on a
+    // ticket of the critical path.  Measured: at the start of the task n=1024 batch 32 0.64 -> 0.72 ms;
+    // before the solve stages (the previous place) 0.65 ms; behind them 0.62 ms (n=300 batch 32
+    // 0.124 -> 0.101 ms, n=1024 batch 16 0.435 -> 0.404 ms; throughput launches unchanged).  Waiting
+    // further, until the consumers have posted the task's publication, is slower again
+    // (n=1024 batch 16 0.443 ms): the next task's own tile then arrives late.
     auto fetch = [&]() {
       int tn;
       if (static_sched) { tn = static_next; static_next += gridDim.x; }
@@ -527,7 +531,6 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           }
         }
         if (ptr_) ptr_[12] = clock64();
-        t_next = fetch();
         if (kind == K_PART) {
           // nothing more to stream: the consumers store the partial sum back in place
         } else if (d.i != d.j) {
@@ -564,6 +567,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           // diagonal task: LT_STAGES stages as scratch for the stacked inverse rows
           load_identity();
         }
+        // the next ticket is drawn only now, behind every load of this task: see `fetch` above
+        t_next = fetch();
         if (ptr_) ptr_[13] = clock64();
       }
       __syncwarp();

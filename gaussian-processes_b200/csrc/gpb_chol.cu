@@ -72,6 +72,7 @@ struct __align__(128) CholSmem {
   int* rel_ptr[2];
   int rel_val[2];
   int taskq[2];
+  int4 taskd[2];                        // the decoded ticket (b, i, j, kind): consumers do not decode again
   int bad_col;
 };
 
@@ -461,14 +462,17 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       int t = __shfl_sync(0xffffffffu, t_next, 0);
       if (t >= task_end) t = -1;
       const int slot = q & 1, qpar = (q >> 1) & 1;
+      TaskDesc d;
+      d.b = d.i = d.j = 0; d.kind = K_PLAIN;
+      if (t >= 0) d = decode_task(g, t, jcache);
       if (lane == 0) {
         if (!mbar_wait_serving(&sm.tq_empty[slot], qpar ^ 1, sm, rs)) atomicExch(&sched->error, 2);
         sm.taskq[slot] = t;
+        sm.taskd[slot] = make_int4(d.b, d.i, d.j, d.kind);
         mbar_arrive(&sm.tq_full[slot]);
       }
       ++q;
       if (t < 0) break;
-      const TaskDesc d = decode_task(g, t, jcache);
       const int k0 = task_k0(g, d);
       const int kind = solve_only ? K_PLAIN : d.kind;
       // L is given: no accumulation for top-square tiles; void task; nothing to pre-accumulate for block 1
@@ -603,13 +607,15 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     const int slot = q & 1, qpar = (q >> 1) & 1;
     if (!mbar_wait(&sm.tq_full[slot], qpar)) atomicExch(&sched->error, 4);
     const int t = sm.taskq[slot];
+    const int4 td = sm.taskd[slot];
     bar_named(1, NCONS);
     if (tid == 0) mbar_arrive(&sm.tq_empty[slot]);
     ++q;
     if (t < 0) break;
     unsigned long long* tr = (TRACE && trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
     if (tr) { tr[0] = globaltimer_ns(); tr[1] = clock64(); }
-    const TaskDesc d = decode_task(g, t, jcache);
+    TaskDesc d;
+    d.b = td.x; d.i = td.y; d.j = td.z; d.kind = td.w;   // decoded by the producer warp
     const int k0 = task_k0(g, d);
     const int kind = solve_only ? K_PLAIN : d.kind;
     if (k0 < 0 || (kind == K_PART && d.j == 1)) continue;

@@ -429,7 +429,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     tma_prefetch_desc(&tmap);
     tma_prefetch_desc(&tmapL);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
     mbar_fence_init();
   }
@@ -608,8 +608,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     if (!mbar_wait(&sm.tq_full[slot], qpar)) atomicExch(&sched->error, 4);
     const int t = sm.taskq[slot];
     const int4 td = sm.taskd[slot];
-    bar_named(1, NCONS);
-    if (tid == 0) mbar_arrive(&sm.tq_empty[slot]);
+    // one arrival per warp, no CTA barrier: the end of the previous task (post_release / factor_block)
+    // already held every warp until all of them were done with Cs
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.tq_empty[slot]);
     ++q;
     if (t < 0) break;
     unsigned long long* tr = (TRACE && trace != nullptr && tid == 0) ? trace + (size_t)t * TRACE_SLOTS : nullptr;
@@ -872,6 +874,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         // L_jj itself (an output only) goes out behind the publication
         if (tid == 0) { __threadfence(); fence_proxy_async(); st_release(done_b + dj, dj + 1); }
         write_L_tile(sm, Ajj, g.ld, tid);
+        bar_named(1, NCONS);           // every warp is done with Cs before the next task may write it
       } else {
         post_release(done_b + dj, dj + 1);
       }

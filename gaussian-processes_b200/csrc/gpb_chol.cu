@@ -944,7 +944,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           for (int nt = 0; nt < 2; ++nt) x[ct][nt][0] = x[ct][nt][1] = 0.0;
         const int kmax = s * SCOLS + (ch + 1) * CTW * 8;   // L^-T(k, c) == 0 for k > c
         const int kfull = kmax - (CTW - 1) * 8;   // below this every column tile of the warp is live
-#pragma unroll (MINB == 1 ? 4 : 2)
+#pragma unroll 4
         for (int kb = 0; kb < kfull; kb += 4) {
           const int k = kb + tq;
           double a[CTW], bb[2];

@@ -366,6 +366,116 @@ __device__ __noinline__ void diag_inverse(CholSmem& sm, double* __restrict__ LT,
   for (int c = 0; c < TILE; ++c) LT[c * LDT + k] = (c >= k) ? row[c] : 0.0;
 }
 
+// Pre-accumulation of a diagonal block (K_PART) as a balanced SYRK, a function of its own so that the
+// ordinary contraction loop keeps its code and registers.  Only fragments on or below the diagonal
+// of the block are ever read (36 of 64): warp 2, whose sub-tile lies strictly above the diagonal,
+// takes tile columns 16..31 of warp 1's full sub-tile (8 fragments each); warps 0 and 3 run the 10
+// lower fragments of their diagonal sub-tiles -- the task lasts 10/16 of the full tile.  The same
+// operations per entry in the same order as the full-tile loop (negated accumulator, k ascending):
+// bit-identical results; the strict upper triangle of the block keeps what it held.
+// Consumes the two tile stages and `nstage` contraction stages of the ring and releases all of them.
+template <int SH>   // 1: two column blocks x four row blocks;  2: lower triangle of a 4 x 4 block grid
+__device__ __forceinline__ void syrk_contract(CholSmem& sm, double* __restrict__ Aij, int ld, uint32_t& stage,
+                                              uint32_t& phase, int pre0, int pre1, int nstage, int lane,
+                                              int cE, int rE, int* error) {
+  constexpr int MT = (SH == 1) ? 2 : 4;
+  const int gq = lane >> 2, tq = lane & 3;
+  auto wait_full = [&](uint32_t st, uint32_t ph) {
+    if (mbar_test_wait(&sm.full[st], ph)) return;
+    if (!mbar_wait(&sm.full[st], ph)) atomicExch(error, 5);
+  };
+  double acc[MT][4][2];
+  {
+    const double* T = &sm.stage[cE < 32 ? pre0 : pre1][0];   // tile columns cE .. of this warp
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+        if (SH != 2 || nt >= mt) {
+          const double2 v = *reinterpret_cast<const double2*>(&T[((cE & 31) + mt * 8 + gq) * LDT + rE + nt * 8 + 2 * tq]);
+          acc[mt][nt][0] = flip_sign(v.x); acc[mt][nt][1] = flip_sign(v.y);
+        }
+  }
+  auto load_frag = [&](const double* P, int ks, double (&a)[MT], double (&bb)[4]) {
+    const int k = ks * 4 + tq;
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) a[mt] = P[k * LDT + cE + mt * 8 + gq];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) bb[nt] = P[(KC + k) * LDT + rE + nt * 8 + gq];
+  };
+  int pend = -1;
+  wait_full(stage, phase);
+  double a[MT], bb[4];
+  load_frag(&sm.stage[stage][0], 0, a, bb);
+#pragma unroll 1
+  for (int it = 0; it < nstage; ++it) {
+    const double* P = &sm.stage[stage][0];
+    uint32_t nst = stage + 1, nph = phase;
+    if (nst == STAGES) { nst = 0; nph ^= 1; }
+    bool next_ready = true;
+#pragma unroll
+    for (int ks = 0; ks < KC / 4; ++ks) {
+      double an[MT], bn[4];
+      if (ks == KC / 4 - 2) next_ready = (it + 1 >= nstage) || mbar_test_wait(&sm.full[nst], nph);
+      if (ks + 1 < KC / 4) {
+        load_frag(P, ks + 1, an, bn);
+      } else if (it + 1 < nstage) {
+        if (!next_ready) wait_full(nst, nph);
+        load_frag(&sm.stage[nst][0], 0, an, bn);
+      } else {
+#pragma unroll
+        for (int i = 0; i < MT; ++i) an[i] = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) bn[i] = 0.0;
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+          if (SH != 2 || nt >= mt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], bb[nt]);
+#pragma unroll
+      for (int i = 0; i < MT; ++i) a[i] = an[i];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) bb[i] = bn[i];
+    }
+    __syncwarp();
+    if (lane == 0) {
+      // the tile stages after the first stage (their LDS fed the flips above, long since issued);
+      // every other stage one stage late (see the ordinary loop)
+      if (it == 0) { mbar_arrive(&sm.empty[pre0]); mbar_arrive(&sm.empty[pre1]); }
+      if (pend >= 0) mbar_arrive(&sm.empty[pend]);
+    }
+    pend = (int)stage;
+    stage = nst; phase = nph;
+  }
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+      if (SH != 2 || nt >= mt)
+        *reinterpret_cast<double2*>(Aij + (size_t)(cE + mt * 8 + gq) * ld + rE + nt * 8 + 2 * tq) =
+            make_double2(flip_sign(acc[mt][nt][0]), flip_sign(acc[mt][nt][1]));
+  __syncwarp();                          // the stores consumed every accumulator: all LDS of the ring are done
+  if (lane == 0 && pend >= 0) mbar_arrive(&sm.empty[pend]);
+}
+__device__ __noinline__ void syrk_task(CholSmem& sm, double* __restrict__ Aij, int ld, uint32_t* stage_io,
+                                       uint32_t* phase_io, int nstage, int tid, int* error) {
+  const int warp = tid >> 5, lane = tid & 31;
+  uint32_t stage = *stage_io, phase = *phase_io;
+  const int pre0 = (int)stage;
+  if (!mbar_test_wait(&sm.full[stage], phase) && !mbar_wait(&sm.full[stage], phase)) atomicExch(error, 5);
+  if (++stage == STAGES) { stage = 0; phase ^= 1; }
+  const int pre1 = (int)stage;
+  if (!mbar_test_wait(&sm.full[stage], phase) && !mbar_wait(&sm.full[stage], phase)) atomicExch(error, 5);
+  if (++stage == STAGES) { stage = 0; phase ^= 1; }
+  // warp: 0 -> block (c 0..31, r 0..31) lower; 3 -> (32.., 32..) lower; 1 -> (c 0..15, r 32..63); 2 -> (c 16..31, r 32..63)
+  if (warp == 1 || warp == 2)
+    syrk_contract<1>(sm, Aij, ld, stage, phase, pre0, pre1, nstage, lane, warp == 1 ? 0 : 16, 32, error);
+  else
+    syrk_contract<2>(sm, Aij, ld, stage, phase, pre0, pre1, nstage, lane, warp == 0 ? 0 : 32, warp == 0 ? 0 : 32, error);
+  *stage_io = stage; *phase_io = phase;
+}
+
 // Deferred publication.  A consumer group that has stored its tile does not wait for the stores
 // to become visible: it posts (counter, value) and moves on to the next task.  The producer lane,
 // which spends most of its time waiting anyway, drains the post: gpu-scope fence (cumulative over
@@ -633,6 +743,16 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     if (solve_only && d.i < g.nt && d.i != d.j) {
       // triangular-solve mode: the factor is an input, its off-diagonal tiles are already final
       if (tid == 0) atomicMax(done_b + d.i, d.j + 1);
+      continue;
+    }
+
+    if (CW == 4 && kind == K_PART) {
+      // diagonal block pre-accumulated as a balanced SYRK (syrk_task), back in place, flag posted
+      if (tr) tr[2] = clock64();
+      syrk_task(sm, Aij, g.ld, &stage, &phase, (kend - k0) * (TILE / KC), tid, &sched->error);
+      if (tr) { tr[3] = tr[4] = tr[5] = clock64(); tr[8] = tr[9] = 0; }
+      post_release(part_b + d.i, 1);
+      if (tr) { tr[6] = clock64(); tr[7] = globaltimer_ns(); }
       continue;
     }
 

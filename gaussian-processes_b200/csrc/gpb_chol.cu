@@ -10,13 +10,19 @@
 //
 // Task (b, i, j) = 64x64 tile (tile row i, tile column j) of proposal b:
 //     acc  = A_ij - sum_{k<j} L_ik L_jk^T          FP64 tensor cores (DMMA.8x8x4), operands streamed
-//                                                   by 1-D bulk async copies (TMA) through a 4-stage
-//                                                   mbarrier ring filled by a dedicated producer warp
+//                                                   by tiled TMA loads through a 4-stage mbarrier
+//                                                   ring filled by a dedicated producer warp
 //     i==j : L_jj = chol(acc), and L_jj^-T by factoring the stacked [acc; I] (one row per thread in
-//            registers, one barrier per column)
+//            registers, two columns per barrier)
 //     i>j  : L_ij = acc * L_jj^-T                   DMMA again
-// Tickets are handed out in topological order (by block column; diagonal first), dependencies are
-// per-tile-row progress counters polled with ld.acquire; every wait is bounded by a watchdog.
+// Task kinds (K_PLAIN / K_DIAG0 / K_PART / K_FUSED below): diagonal blocks are pre-accumulated off the
+// critical path as a balanced SYRK (syrk_task) and factored by the CTA that solves the tile above
+// them; the tile row that only holds the rhs row runs one 8-row fragment ("light" tasks).
+// Tickets are handed out in topological order (by block column), decoded by the producer warp and
+// passed to the consumers through shared memory; dependencies are per-tile-row progress counters
+// polled with ld.acquire; every wait is bounded by a watchdog.  Two instantiations: <TRACE, 2> for
+// throughput launches (two CTAs per SM, 168 registers), <TRACE, 1> for launches bound by the
+// dependency chain (one CTA per SM, no register cap).
 // Summation order is fixed by the task, not by the schedule: results are bit-reproducible.
 //
 // Roofline: trailing contraction n^3/3 flop on the FP64 tensor pipe (37.1 TFLOP/s measured DMMA

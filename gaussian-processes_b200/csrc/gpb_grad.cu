@@ -167,14 +167,17 @@ k_grad_contract(const __grid_constant__ CUtensorMap tmap, Geom g, const GradSpec
         const double* P = &sm.stage[stage][0];
         uint32_t nst = stage + 1, nph = phase;
         if (nst == GSTAGES) { nst = 0; nph ^= 1; }
+        bool next_ready = true;
 #pragma unroll
         for (int ks = 0; ks < GKC / 4; ++ks) {
           // the next k-step's fragments (or the next stage's first) are fetched before these 16 DMMAs issue
           double an[4], bn[4];
+          // the barrier of the next stage is probed one k-step before its result is needed
+          if (ks == GKC / 4 - 2) next_ready = (it + 1 >= nstage) || mbar_test_wait(&sm.full[nst], nph);
           if (ks + 1 < GKC / 4) {
             load_frag(P, ks + 1, an, bn);
           } else if (it + 1 < nstage) {
-            wait_full(nst, nph);
+            if (!next_ready) wait_full(nst, nph);
             load_frag(&sm.stage[nst][0], 0, an, bn);
           } else {
 #pragma unroll

@@ -114,14 +114,14 @@ int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
 
 int finish_timing(gpb_ctx* ctx) {
   CK(cudaEventRecord(ctx->ev[3], ctx->stream));
-  CK(cudaMemcpyAsync(ctx->h_sched, ctx->sched, sizeof(SchedState), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_sched, ctx->sched, SCHED_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   CK(cudaGetLastError());
   for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&ctx->timing[i], ctx->ev[i], ctx->ev[i + 1]);
-  const SchedState s = *ctx->h_sched;
-  if (s.error != 0) {
-    ctx->cuda_err = "scheduler watchdog code " + std::to_string(s.error);
-    cudaMemset(ctx->sched, 0, sizeof(SchedState));
+  const int sched_error = ctx->h_sched->error;
+  if (sched_error != 0) {
+    ctx->cuda_err = "scheduler watchdog code " + std::to_string(sched_error);
+    cudaMemset(ctx->sched, 0, SCHED_HEAD_BYTES);
     return GPB_E_WATCHDOG;
   }
   return GPB_OK;
@@ -143,6 +143,7 @@ const char* gpb_strerror(int status) {
     case GPB_E_UNSUPPORTED: return "unsupported (Matern kernel / dim > 2 are out of scope)";
     case GPB_E_WATCHDOG: return "scheduler watchdog fired";
     case GPB_E_NOTPD: return "covariance matrix not positive definite";
+    case GPB_E_NOCOMM: return "no communicator (NCCL not loadable, or gpb_comm_init_* not called on this context)";
     default: return "unknown status";
   }
 }
@@ -192,7 +193,16 @@ int gpb_ctx_create(int device, gpb_ctx** out) {
   ctx->num_sms = prop.multiProcessorCount;
   cudaError_t e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) {
+    // the flush / gather stream of the MH loop: highest priority, so that its (tiny) copies and the
+    // NCCL kernel are scheduled in the gaps between the iterations' kernels
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    e = cudaStreamCreateWithPriority(&ctx->copy_stream, cudaStreamNonBlocking, hi);
+  }
   for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&ctx->ev[i]);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&ctx->ev_ready[i], cudaEventDisableTiming);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&ctx->ev_flushed[i], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->sched, sizeof(SchedState));
   if (e == cudaSuccess) e = cudaMemset(ctx->sched, 0, sizeof(SchedState));
   if (e == cudaSuccess) e = cudaMallocHost((void**)&ctx->h_sched, sizeof(SchedState));
@@ -205,6 +215,11 @@ void gpb_ctx_destroy(gpb_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+  comm_release(ctx);
+  cudaFree(ctx->mh); cudaFree(ctx->ring); cudaFreeHost(ctx->h_stage);
+  for (int i = 0; i < 2; ++i) { if (ctx->ev_ready[i]) cudaEventDestroy(ctx->ev_ready[i]); if (ctx->ev_flushed[i]) cudaEventDestroy(ctx->ev_flushed[i]); }
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   cudaFree(ctx->mats); cudaFree(ctx->linvt); cudaFree(ctx->done); cudaFree(ctx->info);
   cudaFree(ctx->trace); cudaFree(ctx->hyper); cudaFree(ctx->ll); cudaFree(ctx->aux); cudaFree(ctx->sched);
   cudaFreeHost(ctx->h_hyper); cudaFreeHost(ctx->h_ll); cudaFreeHost(ctx->h_sched);
@@ -318,7 +333,7 @@ static int build_to_host(gpb_ctx* ctx, int n, int dim, const double* x, const gp
   const Geom g = make_geom(n, dim, 0, false, 1);
   int rc = ensure_workspace(ctx, g);
   if (rc) return rc;
-  if (mode == 0) {
+  if (mode != BUILD_DISTANCE) {
     rc = fill_hyper(&ctx->h_hyper[0], terms, nterms, nullptr, 0, dim);
     if (rc) return rc;
   } else {
@@ -327,7 +342,9 @@ static int build_to_host(gpb_ctx* ctx, int n, int dim, const double* x, const gp
   if ((rc = grow(ctx, &ctx->aux, &ctx->aux_doubles, (size_t)n * dim))) return rc;
   CK(cudaMemcpyAsync(ctx->aux, x, sizeof(double) * (size_t)n * dim, cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaMemcpyAsync(ctx->hyper, ctx->h_hyper, sizeof(Hyper), cudaMemcpyHostToDevice, ctx->stream));
-  launch_build(ctx->stream, g, ctx->aux, nullptr, nullptr, ctx->hyper, nugget, ctx->mats, mode, 1);
+  if (mode == BUILD_FAST)   // the lower trapezoid only, as the factorisation reads it; the rest reads as zero
+    CK(cudaMemsetAsync(ctx->mats, 0, sizeof(double) * g.mat_stride, ctx->stream));
+  launch_build(ctx->stream, g, ctx->aux, nullptr, nullptr, ctx->hyper, nugget, ctx->mats, mode, mode != BUILD_FAST);
   ctx->launches += 1;
   CK(cudaMemcpy2DAsync(out, sizeof(double) * n, ctx->mats, sizeof(double) * g.ld, sizeof(double) * n,
                        n, cudaMemcpyDeviceToHost, ctx->stream));
@@ -343,6 +360,15 @@ int gpb_distance_matrix(gpb_ctx* ctx, int n, int dim, const double* x, double* D
 int gpb_build_cov(gpb_ctx* ctx, int n, int dim, const double* x, const gpb_term* terms, int nterms,
                   double nugget, double* K) {
   return build_to_host(ctx, n, dim, x, terms, nterms, nugget, K, 0);
+}
+
+int gpb_build_cov_hot(gpb_ctx* ctx, int n, int dim, const double* x, const gpb_term* terms, int nterms,
+                      double nugget, double* K) {
+  int rc = build_to_host(ctx, n, dim, x, terms, nterms, nugget, K, BUILD_FAST);
+  if (rc) return rc;
+  // diagonal tiles are written whole: clear what lies above the diagonal
+  for (int c = 1; c < n; ++c) std::memset(K + (size_t)c * n, 0, sizeof(double) * c);
+  return GPB_OK;
 }
 
 int gpb_potrf(gpb_ctx* ctx, int n, double* A, int* info) {

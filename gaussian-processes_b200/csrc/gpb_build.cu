@@ -14,30 +14,13 @@
 // (column-major), inputs (x, y: KBs) staged in shared memory.  Algorithmic bytes: 4 n^2 per
 // proposal for the likelihood (lower triangle incl. diagonal tiles), 8 n m for K*.
 #include "gpb_internal.h"
+#include "gpb_cov.cuh"
 
 namespace gpb {
 
 #ifndef GPB_BUILD_MINB
 #define GPB_BUILD_MINB 4
 #endif
-
-__device__ __forceinline__ double cov_of_dist(const Hyper& h, double d) {
-  // KernelFunction.scala:47-55: ps.map(k_i(d)).sum == ((0.0 + k0) + k1) + ...
-  double s = 0.0;
-#pragma unroll 1
-  for (int t = 0; t < h.nterms; ++t) {
-    double v;
-    if (h.kind[t] == GPB_KIND_SE) {
-      double sg = h.p1[t];
-      // KernelFunction.scala:14; explicit _rn ops: the JVM never contracts a*b+c into an FMA
-      v = __dmul_rn(h.p0[t], exp(-__ddiv_rn(__dmul_rn(d, d), __dmul_rn(sg, sg))));
-    } else {
-      v = (d == 0.0) ? h.p0[t] : 0.0;  // KernelFunction.scala:34
-    }
-    s = __dadd_rn(s, v);
-  }
-  return s;
-}
 
 // Hot-path form of the same sum: exp(d2 * (-1/s^2)) with -1/s^2 formed once per CTA -- no square
 // root, no re-squaring, no IEEE division per entry (k_build is FP64-ALU bound on exactly those).  d2 is

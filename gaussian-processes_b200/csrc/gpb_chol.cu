@@ -67,6 +67,11 @@ static_assert(STAGES >= AT_STAGES + 2, "ring too small");
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
 constexpr int TRACE_SLOTS = 14;   // == CHOL_TRACE_SLOTS
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
+#ifndef GPB_PAUSE_TASKS_PER_SM
+#define GPB_PAUSE_TASKS_PER_SM 48
+#endif
+constexpr int PAUSE_TASKS_PER_SM = GPB_PAUSE_TASKS_PER_SM;
+constexpr long long PAUSE_MAX_CLOCKS = 120000LL;      // ~60 us: a pause is advisory and bounded
 
 struct __align__(128) CholSmem {
   double stage[STAGES][STAGE_DOUBLES];  // [0..KC) panel j ("c" rows), [KC..2KC) panel i ("r" rows)
@@ -80,6 +85,8 @@ struct __align__(128) CholSmem {
   int taskq[2];
   int4 taskd[2];                        // the decoded ticket (b, i, j, kind): consumers do not decode again
   int bad_col;
+  int* pause_mine;                      // chain_pause: this CTA's "inside a critical section" flag ...
+  int* pause_other;                     // ... and the flag of the CTA it shares the SM with
 };
 
 size_t chol_smem_bytes() { return sizeof(CholSmem); }
@@ -184,7 +191,12 @@ __global__ void k_chol_reset(Geom g, int* __restrict__ done, int* __restrict__ i
     done[i] = v;
     if (i < g.batch) info[i] = 0;
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) sched->next_task = 0;
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) sched->next_task = 0;
+    for (int e = threadIdx.x; e < SCHED_MAXSM; e += blockDim.x) {
+      sched->smslot[e] = 0; sched->pause[2 * e] = 0; sched->pause[2 * e + 1] = 0;
+    }
+  }
 }
 
 __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* error) {
@@ -535,7 +547,7 @@ template <bool TRACE, int MINB>
 __global__ void __launch_bounds__(NTHREADS, MINB)
 k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapL, Geom g, double* __restrict__ mats, double* __restrict__ linvt, int* __restrict__ done,
              int* __restrict__ info, SchedState* sched, int task_begin, int task_end,
-             int static_sched, int solve_only, unsigned long long* __restrict__ trace) {
+             int static_sched, int solve_only, unsigned long long* __restrict__ trace, int chain_pause) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -548,6 +560,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
     mbar_fence_init();
+    sm.pause_mine = sm.pause_other = nullptr;
+    if (chain_pause) {
+      // which of the (up to two) CTAs of this SM am I?  Arrival order on a per-SM counter.
+      const unsigned sid = smid() % SCHED_MAXSM;
+      const int slot = atomicAdd(&sched->smslot[sid], 1) & 1;
+      sm.pause_mine = &sched->pause[2 * sid + slot];
+      sm.pause_other = &sched->pause[2 * sid + (slot ^ 1)];
+    }
   }
   __syncthreads();
 
@@ -574,6 +594,19 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       return tn;   // raw: clamped at the loop top
     };
     int t_next = (lane == 0) ? fetch() : 0;
+    // chain_pause: do not feed this CTA's contraction while the CTA that shares the SM is inside a
+    // critical section (advisory: bounded, and publications keep being served)
+    int* const pause_mine = sm.pause_mine;
+    int* const pause_other = sm.pause_other;
+    auto hold_while_paused = [&]() {
+      if (pause_other == nullptr || *(volatile int*)pause_other <= 0) return;
+      const long long t0 = clock64();
+      while (*(volatile int*)pause_other > 0) {
+        service_release(sm, rs);
+        if (clock64() - t0 > PAUSE_MAX_CLOCKS) break;
+        __nanosleep(200);
+      }
+    };
     for (;;) {
       int t = __shfl_sync(0xffffffffu, t_next, 0);
       if (t >= task_end) t = -1;
@@ -642,6 +675,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           if (polled) fence_proxy_async();
 #pragma unroll 1
           for (int s = 0; s < TILE / KC; ++s) {
+            hold_while_paused();
             if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
             const int col = kc * TILE + s * KC;
             mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
@@ -672,6 +706,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             // its factorisation
             if (d.j > 0) wait_counter_serving(part_b + d.i, 1, &sched->error, sm, rs);
             fence_proxy_async();
+            // everything the critical section needs exists: the SM is this CTA's until the block is factored
+            if (pause_mine != nullptr) atomicAdd(pause_mine, 1);
 #pragma unroll 1
             for (int s = 0; s < AT_STAGES; ++s) {
               if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
@@ -685,6 +721,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           }
         } else if (!solve_only) {
           // diagonal task: LT_STAGES stages as scratch for the stacked inverse rows
+          if (pause_mine != nullptr) atomicAdd(pause_mine, 1);
           load_identity();
         }
         // the next ticket is drawn only now, behind every load of this task: see `fetch` above
@@ -1004,6 +1041,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       } else {
         post_release(done_b + dj, dj + 1);
       }
+      if (tid == 0 && sm.pause_mine != nullptr) atomicSub(sm.pause_mine, 1);   // end of the critical section
       fence_proxy_async();             // generic writes to the scratch stages before TMA refills them
       __syncwarp();
       if (lane == 0)
@@ -1303,7 +1341,8 @@ long long chol_schedule_task(const Geom& g_in, long long ticket, int* out4) {
 }
 
 int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,
-                SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace) {
+                SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace,
+                int chain_pause) {
   // per host thread (one gpb_ctx per thread): the attribute is set once per device, and the two TMA
   // descriptors are re-encoded only when the workspace or the geometry changed -- both are pure host
   // latency on every small call otherwise
@@ -1349,15 +1388,27 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
     const long long slots = (long long)num_sms * ctas;
     int grid = (int)(total < slots ? total : slots);
+    // Two CTAs per SM, but still few enough tasks per SM that the chain diag(j) -> (j+1, j) -> diag(j+1)
+    // bounds part of the launch: the CTA inside a block column's critical section gets the SM to itself
+    // (see SchedState::pause; its X X^T + factorisation then takes 19.6 instead of 26.6 us).  Measured
+    // (tools/pause_sweep.py, profiles/r02_chain_pause_sweep.txt): n=4096 x 2 proposals -10.7 %, x 3 -3.2 %,
+    // n=2048 x 8 -4.6 %, n=1024 x 32 neutral; a loss once the launch is bound by CTA time (n=1024 x 64
+    // +3.5 %, x 256 +4.3 %) or the chain is short (n=300 x 256 +10 %).  GPB_CHAIN_PAUSE=0|1 overrides.
+    static int env_pause = -2;
+    if (env_pause == -2) { const char* e = getenv("GPB_CHAIN_PAUSE"); env_pause = e ? atoi(e) : -1; }
+    int pause = (ctas == 2 && !solve_only && g.nt >= 16 && total < (long long)PAUSE_TASKS_PER_SM * num_sms) ? 1 : 0;
+    if (chain_pause >= 0) pause = chain_pause;
+    if (env_pause >= 0) pause = env_pause;
+    if (ctas != 2 || num_sms > SCHED_MAXSM) pause = 0;
     if (trace)
       k_chol_tasks<true, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                                                  (int)total, 0, solve_only, trace);
+                                                                                  (int)total, 0, solve_only, trace, pause);
     else if (ctas == 1)
       k_chol_tasks<false, 1><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                                       (int)total, 0, solve_only, trace);
+                                                                       (int)total, 0, solve_only, trace, 0);
     else
       k_chol_tasks<false, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
-                                                                                   (int)total, 0, solve_only, trace);
+                                                                                   (int)total, 0, solve_only, trace, pause);
     ++launches;
   } else {
     // debug / fallback: one launch per ticket phase; every dependency is in an earlier launch
@@ -1365,7 +1416,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
       if (count <= 0) return;
       int grid = (int)(count < 2LL * num_sms ? count : 2LL * num_sms);
       k_chol_tasks<false, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched,
-                                                                                   (int)begin, (int)(begin + count), 1, solve_only, nullptr);
+                                                                                   (int)begin, (int)(begin + count), 1, solve_only, nullptr, 0);
       ++launches;
     };
     run(0, g.batch);

@@ -105,6 +105,8 @@ k_plane_epilogue(Geom g, const double* __restrict__ mats, const double* __restri
 #pragma unroll
     for (int b = 0; b < MAXD; ++b) G[a][b] = 0.0; }
   const size_t r0 = (size_t)g.npad + g.m;
+  mats += (size_t)blockIdx.x * g.mat_stride;          // one CTA per proposal (the MH loop's Gibbs step is batched)
+  out += (size_t)blockIdx.x * (d * d + d);
   for (int c = threadIdx.x; c < g.n; c += blockDim.x) {
     const double* col = mats + (size_t)c * g.ld;
     const double u = col[g.rhs_row];
@@ -146,7 +148,7 @@ k_plane_epilogue(Geom g, const double* __restrict__ mats, const double* __restri
 }
 void launch_plane_epilogue(cudaStream_t st, const Geom& g, const double* mats, const double* rows,
                            double* out) {
-  k_plane_epilogue<<<1, 256, 0, st>>>(g, mats, rows, out);
+  k_plane_epilogue<<<g.batch, 256, 0, st>>>(g, mats, rows, out);
 }
 
 // GaussianProcess.draw (GaussianProcess.scala:67-83) with the Cholesky root: out = mu + L z, one

@@ -37,6 +37,15 @@ struct gpb_ctx {
   long long launches = 0;
   float timing[3] = {0, 0, 0};
   std::string cuda_err;
+  // MH loop (gpb_mh.cu): chain state + stream + output ring; flush path on a second stream
+  double* mh = nullptr;      size_t mh_doubles = 0;     // chain state, host-supplied streams
+  double* ring = nullptr;    size_t ring_doubles = 0;   // 2 segments of T iterations (+ gathered copies)
+  double* h_stage = nullptr; size_t h_stage_doubles = 0;  // pinned staging of the flushed segments
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_flushed[2] = {nullptr, nullptr};
+  // communicator (gpb_comm.cu): ncclComm_t behind a void* so that only gpb_comm.cu needs nccl.h
+  void* comm = nullptr;
+  int comm_rank = 0, comm_nranks = 1;
 };
 
 struct gpb_dataset {
@@ -84,5 +93,8 @@ int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y
 int finish_timing(gpb_ctx* ctx);
 // Launch the factorisation / panel-solve kernel(s) on ctx->stream; counts launches; status out.
 int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only);
+// gpb_comm.cu: all-gather `count` doubles per rank, device to device, on `st` (recv: [nranks][count]).
+int comm_allgather(gpb_ctx* ctx, const double* d_send, double* d_recv, size_t count, cudaStream_t st);
+void comm_release(gpb_ctx* ctx);
 
 }  // namespace gpbh

@@ -5,10 +5,17 @@
 namespace gpb {
 
 // Scheduler state of the factorisation kernel (device memory, zeroed before every launch).
+constexpr int SCHED_MAXSM = 256;
 struct SchedState {
   int next_task;  // atomic ticket
   int error;      // != 0: a watchdog fired (GPB_E_WATCHDOG); kernels drain without waiting
+  // Chain-bound launches with two CTAs per SM (k_chol_tasks, `chain_pause`): a CTA that runs the
+  // critical section of a block column (solve tile (j+1, j), update and factor diag(j+1)) asks the
+  // producer warp of the CTA it shares the SM with to stop feeding its ring for that long.
+  int smslot[SCHED_MAXSM];      // arrival counter per SM: the CTA's slot (0 / 1) on its SM
+  int pause[2 * SCHED_MAXSM];   // pause[2 * smid + slot] != 0: that CTA is inside a critical section
 };
+constexpr size_t SCHED_HEAD_BYTES = 2 * sizeof(int);   // what the host reads back after every call
 
 // k_build modes: the reference's exact operation order (matrix-level gpb_build_cov), the distance
 // matrix, and the hot-path form used by every factorising entry point (gpb_build.cu).
@@ -26,7 +33,7 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 // Returns the number of kernel launches issued.
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done,
                 int* info, SchedState* sched, int mode, int num_sms, int solve_only = 0,
-                unsigned long long* trace = nullptr);
+                unsigned long long* trace = nullptr, int chain_pause = -1);
 constexpr int CHOL_TRACE_SLOTS = 14;
 long long chol_task_count(const Geom& g);
 // ticket -> {proposal, tile row, tile column, kind}; returns the number of tickets
@@ -42,7 +49,7 @@ void launch_ll_epilogue(cudaStream_t st, const Geom& g, const double* mats, cons
                         gpb_ll* out);
 // Plane-mean Gibbs statistics: G = V V^T over the solved design rows, w = X^T u (gpb_epilogue.cu).
 void launch_plane_epilogue(cudaStream_t st, const Geom& g, const double* mats, const double* rows,
-                           double* out /* [design*design + design] */);
+                           double* out /* [batch][design*design + design] */);
 // mu + L z for a factored matrix (GaussianProcess.draw), one CTA per 64 rows.
 void launch_draw(cudaStream_t st, const Geom& g, const double* mats, const double* z, const double* mu,
                  double* out);

@@ -2,6 +2,7 @@
 //   MeanParameters.samplePlane  MeanParameters.scala:74-103  -> gpb_plane_stats / gpb_sample_plane
 //   GaussianProcess.draw        GaussianProcess.scala:67-83  -> gpb_draw (Cholesky root, see header)
 #include "gpb_host.h"
+#include "gpb_plane.h"
 
 using namespace gpb;
 using namespace gpbh;
@@ -42,29 +43,6 @@ int gpb_plane_stats(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, 
   return GPB_OK;
 }
 
-// d x d host algebra of the Gibbs step (d = dim + 1 <= 4): Breeze `\` on a square matrix is an LU
-// solve with partial pivoting, `cholesky` the lower factor.
-static bool lu_solve(int d, const double* A, const double* b, double* x) {
-  double M[4][5];
-  for (int i = 0; i < d; ++i) { for (int j = 0; j < d; ++j) M[i][j] = A[i * d + j]; M[i][d] = b[i]; }
-  for (int c = 0; c < d; ++c) {
-    int p = c;
-    for (int i = c + 1; i < d; ++i) if (std::fabs(M[i][c]) > std::fabs(M[p][c])) p = i;
-    if (M[p][c] == 0.0) return false;
-    if (p != c) for (int j = 0; j <= d; ++j) std::swap(M[p][j], M[c][j]);
-    for (int i = c + 1; i < d; ++i) {
-      const double f = M[i][c] / M[c][c];
-      for (int j = c; j <= d; ++j) M[i][j] -= f * M[c][j];
-    }
-  }
-  for (int i = d - 1; i >= 0; --i) {
-    double s = M[i][d];
-    for (int j = i + 1; j < d; ++j) s -= M[i][j] * x[j];
-    x[i] = s / M[i][i];
-  }
-  return true;
-}
-
 int gpb_sample_plane(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms, int nterms,
                      double nugget, int d, const double* X, double prior_mean, double prior_var,
                      const double* z, double* beta, int* info) {
@@ -75,28 +53,8 @@ int gpb_sample_plane(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_term* terms,
   if (rc) return rc;
   if (info) *info = h_info;
   if (h_info != 0) return GPB_OK;  // kxx not positive definite: the reference throws from cholesky
-  double prec[16], rhs[4], mean[4], root[16] = {0};
-  for (int i = 0; i < d; ++i) {
-    for (int j = 0; j < d; ++j) prec[i * d + j] = G[i * d + j] + (i == j ? 1.0 / prior_var : 0.0);
-    rhs[i] = (1.0 / prior_var) * prior_mean + w[i];   // priorPrec * fill(mean) + x.t * u  (:94-95)
-  }
-  if (!lu_solve(d, prec, rhs, mean)) { if (info) *info = -1; return GPB_OK; }
-  for (int j = 0; j < d; ++j) {                       // root = cholesky(prec)  (:97)
-    double s = prec[j * d + j];
-    for (int k = 0; k < j; ++k) s -= root[j * d + k] * root[j * d + k];
-    if (!(s > 0.0)) { if (info) *info = j + 1; return GPB_OK; }
-    root[j * d + j] = std::sqrt(s);
-    for (int i = j + 1; i < d; ++i) {
-      double t = prec[i * d + j];
-      for (int k = 0; k < j; ++k) t -= root[i * d + k] * root[j * d + k];
-      root[i * d + j] = t / root[j * d + j];
-    }
-  }
-  for (int i = 0; i < d; ++i) {                       // beta = mean + root \ z  (:99)
-    double s = z[i];
-    for (int k = 0; k < i; ++k) s -= root[i * d + k] * (beta[k] - mean[k]);
-    beta[i] = mean[i] + s / root[i * d + i];
-  }
+  const int pinfo = plane_draw(d, G, w, prior_mean, prior_var, z, beta);
+  if (pinfo != 0 && info) *info = pinfo;
   return GPB_OK;
 }
 

@@ -23,8 +23,14 @@ EXPORTS = [
     "gpb_philox_streams", "gpb_strerror", "gpb_last_cuda_error", "gpb_launch_count",
     "gpb_last_timing", "gpb_set_sched", "gpb_set_trace", "gpb_get_trace", "gpb_version",
     "gpb_plane_stats", "gpb_sample_plane", "gpb_draw", "gpb_mll_gradient",
-    "gpb_schedule_task",
+    "gpb_schedule_task", "gpb_build_cov_hot", "gpb_mh_run_ex", "gpb_mh_run_host", "gpb_philox_streams_device",
+    "gpb_comm_unique_id", "gpb_comm_init_rank", "gpb_comm_init_all", "gpb_comm_destroy", "gpb_comm_info",
+    "gpb_comm_shard", "gpb_gather",
 ]
+RNG_HOST, RNG_PHILOX = 0, 1
+SMALL_AUTO, SMALL_OFF = 0, 1
+E_NOTPD, E_NOCOMM = -7, -8
+COMM_ID_BYTES = 128
 
 
 class Term(C.Structure):
@@ -41,6 +47,23 @@ class MhOpts(C.Structure):
                 ("nugget", C.c_double)]
 
 
+class MhConfig(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("formula", C.c_int), ("on_notpd", C.c_int), ("rng", C.c_int),
+                ("delta", C.c_double), ("nugget", C.c_double), ("seed", C.c_ulonglong), ("chain0", C.c_int),
+                ("mean_step", C.c_int), ("mean_prior_mean", C.c_double), ("mean_prior_var", C.c_double),
+                ("mean_nugget", C.c_double), ("flush_every", C.c_int), ("gather", C.c_int),
+                ("total_chains", C.c_int), ("small_n", C.c_int)]
+
+
+class MhResult(C.Structure):
+    _fields_ = [("info", C.c_int), ("stopped_chains", C.c_int), ("path", C.c_int), ("flushes", C.c_int),
+                ("device_ms", C.c_float)]
+
+
+PROPOSE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double))
+LOG_PRIOR_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double))
+
+
 class GpbError(RuntimeError):
     def __init__(self, status, msg):
         super().__init__(f"gpb200 status {status}: {msg}")
@@ -52,6 +75,24 @@ _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
 
 
+def _prefer_bundled_nccl():
+    """libgpb200.so binds NCCL at run time (gpb_comm_*).  In a Python process that also imports torch,
+    both must end up on the SAME libnccl.so.2: a system NCCL loaded first would shadow the (newer) one
+    torch is linked against.  Point GPB_NCCL_LIB at the wheel's copy unless the caller chose one."""
+    if os.environ.get("GPB_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for loc in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(loc, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["GPB_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
+
+
 def load():
     """Load libgpb200.so; raises (never falls back) when it has not been built."""
     global _lib
@@ -61,6 +102,7 @@ def load():
         raise ImportError(
             f"{LIB_PATH} not found: build it with `make -C gaussian-processes_b200/csrc` "
             "(or __graft_entry__.build()); gpb200 has no CPU fallback")
+    _prefer_bundled_nccl()
     L = C.CDLL(LIB_PATH)
     L.gpb_strerror.restype = C.c_char_p
     L.gpb_last_cuda_error.restype = C.c_char_p
@@ -91,6 +133,19 @@ def load():
     L.gpb_mh_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Term), C.c_int,
                              _dp, C.c_int, _dp, C.POINTER(MhOpts), _dp, _dp, _dp, _dp, _ip, _ip]
     L.gpb_philox_streams.argtypes = [C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_philox_streams_device.argtypes = [C.c_void_p, C.c_ulonglong, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+    L.gpb_mh_run_ex.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(MhConfig), C.c_int, C.c_int, C.POINTER(Term),
+                                C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp, _dp, _dp, _ip, _ip, C.POINTER(MhResult)]
+    L.gpb_mh_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Term), C.c_int, _dp, C.c_int,
+                                  C.POINTER(MhOpts), PROPOSE_FN, LOG_PRIOR_FN, C.c_void_p, _dp, _dp, _dp, _ip, _ip]
+    L.gpb_build_cov_hot.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, C.POINTER(Term), C.c_int, C.c_double, _dp]
+    L.gpb_comm_unique_id.argtypes = [C.c_void_p]
+    L.gpb_comm_init_rank.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    L.gpb_comm_init_all.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    L.gpb_comm_destroy.argtypes = [C.c_void_p]
+    L.gpb_comm_info.argtypes = [C.c_void_p, _ip, _ip]
+    L.gpb_comm_shard.argtypes = [C.c_int, C.c_int, C.c_int, _ip, _ip]
+    L.gpb_gather.argtypes = [C.c_void_p, _dp, C.c_int, _dp]
     L.gpb_plane_stats.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
                                   _dp, _dp, _dp, _ip]
     L.gpb_sample_plane.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
@@ -210,6 +265,45 @@ class Context:
         out = np.empty((n, n), dtype=np.float64)
         self._check(self.L.gpb_build_cov(self.h, n, dim, _ptr(xs), arr, nterms, float(nugget), _ptr(out)))
         return out.T
+
+    def build_cov_hot(self, x, terms, nugget=0.0):
+        """The matrix in the form the factorisation consumes (k_build hot-path mode): lower triangle."""
+        xs, dim = x_soa(x)
+        n = xs.shape[1]
+        arr, nterms = terms_array([terms])
+        out = np.empty((n, n), dtype=np.float64)
+        self._check(self.L.gpb_build_cov_hot(self.h, n, dim, _ptr(xs), arr, nterms, float(nugget), _ptr(out)))
+        return out.T
+
+    # ---- communicator (one rank per Context) ----
+    def comm_init_rank(self, nranks, rank, uid):
+        buf = C.create_string_buffer(bytes(uid), COMM_ID_BYTES)
+        self._check(self.L.gpb_comm_init_rank(self.h, int(nranks), int(rank), buf))
+
+    def comm_destroy(self):
+        self._check(self.L.gpb_comm_destroy(self.h))
+
+    def comm_info(self):
+        """(rank, nranks, has_communicator)"""
+        r, n = C.c_int(0), C.c_int(1)
+        st = self.L.gpb_comm_info(self.h, C.byref(r), C.byref(n))
+        return r.value, n.value, st == 0
+
+    def gather(self, values):
+        """All-gather of a vector of doubles through the context's communicator: (nranks, count)."""
+        v = as_f64(values).ravel()
+        _, nranks, ok = self.comm_info()
+        out = np.empty((nranks, v.size))
+        self._check(self.L.gpb_gather(self.h, _ptr(v), int(v.size), _ptr(out)))
+        return out
+
+    def philox_streams_device(self, seed, chain0, chains, iters, P):
+        """The streams exactly as the device generator of mh_run_ex(rng=RNG_PHILOX) consumes them."""
+        z = np.empty((iters, chains, P))
+        u = np.empty((iters, chains))
+        self._check(self.L.gpb_philox_streams_device(self.h, int(seed), int(chain0), int(chains), int(iters), int(P),
+                                                     _ptr(z), _ptr(u)))
+        return z, u
 
     def potrf(self, K):
         K = np.asarray(K, dtype=np.float64)
@@ -383,6 +477,115 @@ class Dataset:
             raise GpbError(st, f"proposal covariance not positive definite (info={info.value})")
         ctx._check(st)
         return states, ll, acc, info.value
+
+
+    def mh_run_ex(self, init_term_lists, ig, delta, iters, z=None, u=None, beta0=None, design=None,
+                  nugget=1e-3, formula=FORMULA_AS_PARSED, on_notpd=0, rng=RNG_HOST, seed=0, chain0=0,
+                  mean_step=False, mean_prior=(0.0, 1.0), mean_nugget=1e-6, flush_every=0, gather=False,
+                  total_chains=0, small_n=SMALL_AUTO, raise_on_notpd=True):
+        """gpb_mh_run_ex: the Mcmc.sample iteration for len(init_term_lists) chains on this device.
+        z: (iters, chains, P [+ d]) / u: (iters, chains) for rng=RNG_HOST; beta0: (chains, nbeta);
+        design: (n, d) design matrix (mean_step).  Returns a dict: states (iters, C, W), ll, accept
+        (iters, C), stop (C,), info, stopped_chains, path, flushes, device_ms, status."""
+        ctx = self.ctx
+        arr, nterms = terms_array(init_term_lists)
+        chains = len(init_term_lists)
+        igv = as_f64(ig)
+        P = igv.shape[0]
+        if igv.shape != (P, 2) or P != sum(2 if t[0] == KIND_SE else 1 for t in init_term_lists[0]):
+            raise ValueError("ig must hold (shape, scale) for each of the P kernel parameters")
+        bv = as_f64(beta0) if beta0 is not None and len(beta0) else None
+        nbeta = 0 if bv is None else bv.shape[1]
+        if bv is not None and bv.shape != (chains, nbeta):
+            raise ValueError("beta0 must be (chains, nbeta)")
+        d = nbeta if mean_step else 0
+        W = P + d
+        zv = uv = None
+        if rng == RNG_HOST:
+            zv, uv = as_f64(z), as_f64(u)
+            if uv.shape != (iters, chains) or zv.shape != (iters, chains, P + d):
+                raise ValueError("stream shapes do not match (iters, chains, P + d)")
+        dv = None
+        if mean_step:
+            dv = np.ascontiguousarray(np.asarray(design, dtype=np.float64).T)   # [d][n]
+            if dv.shape != (d, self.n):
+                raise ValueError("design must be (n, nbeta)")
+        cfg = MhConfig(C.sizeof(MhConfig), int(formula), int(on_notpd), int(rng), float(delta), float(nugget),
+                       int(seed), int(chain0), int(bool(mean_step)), float(mean_prior[0]), float(mean_prior[1]),
+                       float(mean_nugget), int(flush_every), int(bool(gather)), int(total_chains), int(small_n))
+        Cn = total_chains if gather else chains
+        states = np.empty((iters, Cn, W)); ll = np.empty((iters, Cn))
+        acc = np.empty((iters, Cn), dtype=np.int32); stop = np.empty(Cn, dtype=np.int32)
+        res = MhResult()
+        st = ctx.L.gpb_mh_run_ex(ctx.h, self.h, C.byref(cfg), chains, int(iters), arr, nterms,
+                                 _ptr(bv) if bv is not None else None, nbeta, _ptr(igv),
+                                 _ptr(zv) if zv is not None else None, _ptr(uv) if uv is not None else None,
+                                 _ptr(dv) if dv is not None else None, _ptr(states), _ptr(ll),
+                                 acc.ctypes.data_as(_ip), stop.ctypes.data_as(_ip), C.byref(res))
+        if st == E_NOTPD and raise_on_notpd:  # the reference throws from cholesky on that chain
+            raise GpbError(st, f"proposal covariance not positive definite (info={res.info}, "
+                               f"{res.stopped_chains} chain(s) stopped)")
+        if st != E_NOTPD:
+            ctx._check(st)
+        return {"states": states, "ll": ll, "accept": acc, "stop": stop, "info": res.info,
+                "stopped_chains": res.stopped_chains, "path": res.path, "flushes": res.flushes,
+                "device_ms": res.device_ms, "status": st}
+
+    def mh_run_host(self, init_term_lists, propose, log_prior, u, beta=(), nugget=1e-3,
+                    formula=FORMULA_AS_PARSED, on_notpd=0):
+        """gpb_mh_run_host: arbitrary host closures.  propose(iter, cur (chains, P)) -> (chains, P);
+        log_prior(params (chains, P)) -> (chains,).  u: (iters, chains)."""
+        ctx = self.ctx
+        arr, nterms = terms_array(init_term_lists)
+        chains = len(init_term_lists)
+        P = sum(2 if t[0] == KIND_SE else 1 for t in init_term_lists[0])
+        uv = as_f64(u)
+        iters = uv.shape[0]
+        bv = as_f64(beta) if len(beta) else None
+
+        def _prop(_user, it, nch, cur, nxt):
+            a = np.ctypeslib.as_array(cur, shape=(nch, P))
+            np.ctypeslib.as_array(nxt, shape=(nch, P))[:] = np.asarray(propose(it, a.copy()), dtype=np.float64)
+
+        def _prior(_user, nch, par, out):
+            a = np.ctypeslib.as_array(par, shape=(nch, P))
+            np.ctypeslib.as_array(out, shape=(nch,))[:] = np.asarray(log_prior(a.copy()), dtype=np.float64)
+
+        opts = MhOpts(int(formula), int(on_notpd), 0.0, float(nugget))
+        states = np.empty((iters, chains, P)); ll = np.empty((iters, chains)); acc = np.empty((iters, chains), dtype=np.int32)
+        info = C.c_int(0)
+        st = ctx.L.gpb_mh_run_host(ctx.h, self.h, chains, iters, arr, nterms, _ptr(bv) if bv is not None else None,
+                                   0 if bv is None else bv.shape[0], C.byref(opts), PROPOSE_FN(_prop), LOG_PRIOR_FN(_prior),
+                                   None, _ptr(uv), _ptr(states), _ptr(ll), acc.ctypes.data_as(_ip), C.byref(info))
+        if st == E_NOTPD:
+            raise GpbError(st, f"proposal covariance not positive definite (info={info.value})")
+        ctx._check(st)
+        return states, ll, acc, info.value
+
+
+def comm_unique_id():
+    """gpb_comm_unique_id: the 128-byte id rank 0 hands to the other ranks."""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    st = load().gpb_comm_unique_id(buf)
+    if st != 0:
+        raise GpbError(st, load().gpb_strerror(st).decode())
+    return buf.raw
+
+
+def comm_init_all(contexts):
+    """gpb_comm_init_all: communicators for a list of Contexts (one per device) from one thread."""
+    arr = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    st = load().gpb_comm_init_all(arr, len(contexts))
+    if st != 0:
+        raise GpbError(st, load().gpb_strerror(st).decode())
+
+
+def comm_shard(total, nranks, rank):
+    f, c = C.c_int(0), C.c_int(0)
+    st = load().gpb_comm_shard(int(total), int(nranks), int(rank), C.byref(f), C.byref(c))
+    if st != 0:
+        raise GpbError(st, "bad shard arguments")
+    return f.value, c.value
 
 
 def schedule(n, appended=1, batch=1):

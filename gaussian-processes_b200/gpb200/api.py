@@ -558,7 +558,10 @@ class KernelParameters:
             lln, llo = llf.batch([nxt, p])
             new_ll = prior(nxt.kernelParameters) + lln
             old_ll = prior(p.kernelParameters) + llo
-            a = min(1.0, math.exp(min(new_ll - old_ll, 700.0)))
+            # Breeze metropolis on the JVM: scala.math.min propagates NaN and `u < NaN` is false, so a NaN
+            # on either side rejects (Python's min(1.0, nan) would return 1.0 and always accept)
+            dl = new_ll - old_ll
+            a = min(1.0, math.exp(min(dl, 700.0))) if dl == dl else float("nan")
             u = rng.uniform()
             return nxt if u < a else p
 

@@ -34,6 +34,7 @@ extern "C" {
 #define GPB_E_UNSUPPORTED (-5) /* e.g. Matern term, dim > 2 */
 #define GPB_E_WATCHDOG (-6)    /* scheduler watchdog fired (internal error, never a hang) */
 #define GPB_E_NOTPD (-7)       /* used only by calls that have no info out-parameter */
+#define GPB_E_NOCOMM (-8)      /* NCCL unavailable, or the ctx has no communicator (gpb_comm_*) */
 
 #define GPB_KIND_SE 0    /* SquaredExp(h, sigma)   KernelParameters.scala:21-35 */
 #define GPB_KIND_WHITE 1 /* White(sigma)           KernelParameters.scala:53-67 */
@@ -106,6 +107,11 @@ int gpb_distance_matrix(gpb_ctx *ctx, int n, int dim, const double *x, double *D
  * K: [n*n], full symmetric matrix. */
 int gpb_build_cov(gpb_ctx *ctx, int n, int dim, const double *x, const gpb_term *terms, int nterms,
                   double nugget, double *K);
+/* The same matrix in the form every factorising entry point consumes (k_build's hot-path mode:
+ * h exp(d^2 (-1/s^2)), no sqrt / re-squaring / division per entry): lower triangle (rows >= columns)
+ * of K + nugget I, strict upper triangle zero.  For entrywise parity tests of the hot path. */
+int gpb_build_cov_hot(gpb_ctx *ctx, int n, int dim, const double *x, const gpb_term *terms, int nterms,
+                      double nugget, double *K);
 /* breeze.linalg.cholesky call sites GaussianProcess.scala:123, Predict.scala:69.  A: [n*n] in,
  * lower factor with zeroed upper triangle out. */
 int gpb_potrf(gpb_ctx *ctx, int n, double *A, int *info);
@@ -120,15 +126,25 @@ int gpb_trsm_upper(gpb_ctx *ctx, int n, int nrhs, const double *U, double *B);
  * (examples/.../SimulatedGp.scala:115-151): log-normal random walk with step `delta`, independent
  * InverseGamma(shape, scale) priors per parameter.  Explicit RNG streams:
  *   z  [iters][chains][P] standard normals, uu [iters][chains] uniforms.
- * init: [chains][nterms]; ig: [P][2].  The whole loop is device resident: one proposal batch per
- * iteration, ll(t) cached (1 factorisation / iteration / chain; the reference does 2).
+ * init: [chains][nterms]; beta: [nbeta] plane coefficients shared by all chains (fixed); ig: [P][2].
+ * The whole loop is device resident: one proposal batch per iteration, ll(t) cached
+ * (1 factorisation / iteration / chain; the reference does 2).
  * out_states [iters][chains][P], out_ll [iters][chains] (prior + loglik after the step),
- * out_accept [iters][chains].  info_out (may be NULL): first non-PD info seen (the reference throws
- * there; the chain then rejects that proposal when on_notpd == 1, or the call stops with
- * GPB_E_NOTPD when on_notpd == 0, the default that mirrors the reference). */
+ * out_accept [iters][chains].
+ * Accept rule, exactly Breeze's: u < min(1, exp(new - old)) with JVM NaN semantics -- a NaN on
+ * either side rejects (scala.math.min propagates NaN and `u < NaN` is false).
+ * Proposal whose covariance is not positive definite (the reference throws from `cholesky` on that
+ * chain's thread and the chain ends there; the other chains are separate threads and carry on):
+ *   on_notpd == 0 (mirror, default): that chain STOPS.  Its rows from the failing iteration on hold
+ *       NaN states / NaN ll / accept 0; the other chains run to the end; the call then returns
+ *       GPB_E_NOTPD and *info_out = the LAPACK info of the first failure (gpb_mh_run_ex also returns
+ *       the iteration at which each chain stopped).
+ *   on_notpd == 1: the proposal is rejected and the chain continues; the call returns GPB_OK and
+ *       *info_out = the first info seen.
+ * This entry point is gpb_mh_run_ex with host streams, a fixed mean and no gather. */
 typedef struct {
   int formula;  /* GPB_FORMULA_* */
-  int on_notpd; /* 0 = stop with GPB_E_NOTPD (mirror), 1 = treat as reject */
+  int on_notpd; /* 0 = the failing chain stops, GPB_E_NOTPD (mirror); 1 = treat as reject */
   double delta;
   double nugget;
 } gpb_mh_opts;
@@ -138,10 +154,121 @@ int gpb_mh_run(gpb_ctx *ctx, const gpb_dataset *ds, int chains, int iters, const
                const double *z, const double *uu, double *out_states, double *out_ll,
                int *out_accept, int *info_out);
 
-/* Counter-based streams (Philox4x32-10, key = (seed, chain), counter = (iter, slot)) for callers
- * that do not bring their own: fills z [iters][chains][P] and uu [iters][chains] on the host. */
+/* The full Mcmc.sample iteration (Mcmc.scala:63-76) for many chains, device resident:
+ *   step = KernelParameters.sample compose MeanParameters.sample   (mean Gibbs step FIRST, :73)
+ * mean_step == 1 (Plane mean, MeanParameters.sample / samplePlane, MeanParameters.scala:74-121): every
+ *   iteration first draws beta from its full conditional -- kxx = K(current kernel parameters) +
+ *   mean_nugget I (1e-6 in the reference, :84), raw y (:91), Gaussian(mean_prior_mean,
+ *   mean_prior_var) prior on every coefficient, `design` = the d = nbeta design-matrix columns [d][n]
+ *   exactly as makeDesignMatrix lays them out (:55-65, its layout quirk included); the design rows
+ *   ride the factorisation (X^T K^-1 X = V V^T) and the d x d algebra runs in a kernel -- then runs
+ *   the Metropolis step on the kernel parameters with BOTH log-likelihoods evaluated at the new beta
+ *   (Breeze's metropolis re-evaluates ll(t); with a moving mean the cached value would be stale):
+ *   three factorisations per chain and iteration, like the reference.
+ *   Streams per (iteration, chain): zdim = P + d normals -- [0, P) the proposal, [P, P + d) the Gibbs
+ *   draw -- and one uniform.  States carry W = P + d values: kernel parameters then beta, the column
+ *   order of the examples' chain files (SimulatedGp.scala:159-160).
+ * mean_step == 0: fixed beta per chain (beta0 [chains][nbeta], or NULL / nbeta = 0 for the Zero mean),
+ *   zdim = W = P, one factorisation per chain and iteration.
+ * rng: GPB_RNG_HOST  z [iters][chains][zdim], uu [iters][chains] supplied by the caller;
+ *      GPB_RNG_PHILOX generated on the device, Philox4x32-10, key = seed, counter = (iteration,
+ *      slot, chain0 + chain, stream) -- the layout of gpb_philox_streams; z and uu are ignored.  The
+ *      uniforms are bit-identical to gpb_philox_streams; the normals go through the device's log /
+ *      sincos (<= 2 ulp from the host generator): gpb_philox_streams_device returns exactly what the
+ *      loop consumes, for parity runs against a host implementation.
+ * Output ring: chain outputs are written to a device ring and flushed every `flush_every`
+ *   iterations (default 32; device memory does not grow with `iters`) on a second stream, overlapped
+ *   with the following iterations.
+ * gather == 1 (needs gpb_comm_init_rank / gpb_comm_init_all on this ctx): this ctx runs `chains` of
+ *   `total_chains` chains (block partition: rank r owns chains [first_r, first_r + count_r), see
+ *   gpb_comm_shard); every flush all-gathers the ring segments device to device with NCCL and every
+ *   rank receives the outputs of ALL chains: out_* are [iters][total_chains][...].  chain0 must be
+ *   this rank's first_r.
+ * small_n: GPB_SMALL_AUTO runs systems with n <= 64 (no mean step) as ONE launch -- one CTA per
+ *   chain walks all iterations, matrix in shared memory (the shipped example thins to n = 20,
+ *   SimulatedGp.scala:112); GPB_SMALL_OFF forces the general path. */
+#define GPB_RNG_HOST 0
+#define GPB_RNG_PHILOX 1
+#define GPB_SMALL_AUTO 0
+#define GPB_SMALL_OFF 1
+typedef struct {
+  int struct_size; /* sizeof(gpb_mh_config): lets the struct grow without breaking callers */
+  int formula;     /* GPB_FORMULA_* */
+  int on_notpd;    /* see gpb_mh_run */
+  int rng;         /* GPB_RNG_* */
+  double delta;    /* proposal step (SimulatedGp.scala:115-130) */
+  double nugget;   /* 1e-3 (GaussianProcess.scala:117) */
+  unsigned long long seed; /* GPB_RNG_PHILOX */
+  int chain0;      /* global index of this ctx's first chain (Philox counter; gather offset) */
+  int mean_step;   /* 0 | 1 */
+  double mean_prior_mean, mean_prior_var; /* priorMean: Gaussian (Mcmc.scala:66) */
+  double mean_nugget;                     /* 1e-6 (MeanParameters.scala:84) */
+  int flush_every; /* iterations per ring segment; <= 0: default */
+  int gather;      /* 0 | 1 */
+  int total_chains;/* gather: chains over all ranks */
+  int small_n;     /* GPB_SMALL_* */
+} gpb_mh_config;
+
+typedef struct {
+  int info;            /* first LAPACK info > 0 seen on any chain (0: none) */
+  int stopped_chains;  /* chains that stopped on a non-PD proposal (on_notpd == 0) */
+  int path;            /* 0 general (k_build / k_chol_tasks per iteration), 1 one-launch small-n kernel */
+  int flushes;         /* ring flushes (and all-gathers when gather == 1) */
+  float device_ms;     /* device time of the loop (CUDA events on the ctx stream) */
+} gpb_mh_result;
+
+/* out_states [iters][C][W], out_ll [iters][C], out_accept [iters][C], out_stop [C] (may be NULL):
+ * iteration at which the chain stopped, -1 = ran to the end; C = gather ? total_chains : chains. */
+int gpb_mh_run_ex(gpb_ctx *ctx, const gpb_dataset *ds, const gpb_mh_config *cfg, int chains, int iters,
+                  const gpb_term *init, int nterms, const double *beta0, int nbeta, const double *ig,
+                  const double *z, const double *uu, const double *design, double *out_states,
+                  double *out_ll, int *out_accept, int *out_stop, gpb_mh_result *res);
+
+/* Generic prior / proposal (KernelParameters.sample takes arbitrary closures,
+ * KernelParameters.scala:231-235): the host supplies them as callbacks, the device evaluates the
+ * likelihoods.  Per iteration: propose(user, iter, chains, cur [chains][P], next [chains][P]) fills the
+ * proposals; log_prior(user, chains, params [chains][P], out [chains]) their log prior densities; one
+ * gpb_loglik_batch over all chains; accept with uu [iters][chains] (Breeze's rule).  One ABI-internal
+ * round trip per iteration -- the price of host closures.  Same outputs as gpb_mh_run. */
+typedef void (*gpb_propose_fn)(void *user, int iter, int chains, const double *cur, double *next);
+typedef void (*gpb_log_prior_fn)(void *user, int chains, const double *params, double *out);
+int gpb_mh_run_host(gpb_ctx *ctx, const gpb_dataset *ds, int chains, int iters, const gpb_term *init,
+                    int nterms, const double *beta, int nbeta, const gpb_mh_opts *opts,
+                    gpb_propose_fn propose, gpb_log_prior_fn log_prior, void *user, const double *uu,
+                    double *out_states, double *out_ll, int *out_accept, int *info_out);
+
+/* Counter-based streams (Philox4x32-10, key = seed, counter = (iter, slot, chain, stream)) for
+ * callers that do not bring their own: fills z [iters][chains][P] and uu [iters][chains] on the host. */
 int gpb_philox_streams(unsigned long long seed, int chain0, int chains, int iters, int P, double *z,
                        double *uu);
+/* The same streams as the device generator of gpb_mh_run_ex (GPB_RNG_PHILOX) produces them. */
+int gpb_philox_streams_device(gpb_ctx *ctx, unsigned long long seed, int chain0, int chains, int iters,
+                              int P, double *z, double *uu);
+
+/* ---- multi-GPU: chains shard across devices, one gather ------------------------ */
+/* The reference runs its chains in parallel with Streaming.writeParallelChain (call sites
+ * examples/.../SimulatedGp.scala:163-165, TemperatureDlm.scala:353-358).  Here chains shard across the
+ * GPUs of one box, one gpb_ctx per device -- one per process under torchrun, or one per JVM thread --
+ * and the only exchange is the all-gather of accepted states, log-likelihoods and accept flags
+ * (NCCL over NVLink), device to device, inside gpb_mh_run_ex.
+ *   gpb_comm_unique_id : rank 0 creates the 128-byte id and hands it to the other ranks by its own
+ *                        means (torch.distributed store, a JVM field, ...).
+ *   gpb_comm_init_rank : every rank, concurrently, with its own ctx.
+ *   gpb_comm_init_all  : single process, one thread: communicators for ctxs[0..n) at once
+ *                        (ncclCommInitAll); the ctxs are then driven from n threads.
+ *   gpb_comm_shard     : the block partition gpb_mh_run_ex assumes: first chain and count of `rank`.
+ *   gpb_gather         : all-gather of `count` doubles per rank through the same communicator (host
+ *                        buffers; e.g. the log-likelihoods of sharded proposal batches).  recv: [nranks][count].
+ * NCCL is loaded at run time (dlopen libnccl.so.2): without it these calls return GPB_E_NOCOMM and
+ * everything single-GPU keeps working. */
+#define GPB_COMM_ID_BYTES 128
+int gpb_comm_unique_id(void *id128);
+int gpb_comm_init_rank(gpb_ctx *ctx, int nranks, int rank, const void *id128);
+int gpb_comm_init_all(gpb_ctx **ctxs, int n);
+int gpb_comm_destroy(gpb_ctx *ctx);
+int gpb_comm_info(const gpb_ctx *ctx, int *rank, int *nranks);
+int gpb_comm_shard(int total, int nranks, int rank, int *first, int *count);
+int gpb_gather(gpb_ctx *ctx, const double *send, int count, double *recv);
 
 /* ---- "next" rows of the scope table ------------------------------------------ */
 /* MeanParameters.samplePlane(prior, obs, xs, dist, p)  MeanParameters.scala:74-103, the Gibbs step

@@ -371,8 +371,11 @@ struct KernelSampler {
     return [ll, prior, prop](const Parameters& p, const std::vector<double>& z, double u) {
       Parameters nxt{p.meanParameters, prop(p.kernelParameters, z)};
       std::vector<double> v = ll.batch({nxt, p});
-      const double a = std::min(1.0, std::exp(std::min(prior(nxt.kernelParameters) + v[0] - prior(p.kernelParameters) - v[1], 700.0)));
-      return u < a ? nxt : p;
+      // JVM semantics of Breeze's metropolis: a NaN difference rejects (scala.math.min propagates NaN,
+      // `u < NaN` is false); std::min(1.0, NaN) would return 1.0 and always accept
+      const double dl = prior(nxt.kernelParameters) + v[0] - prior(p.kernelParameters) - v[1];
+      const bool accept = (dl == dl) && u < std::min(1.0, std::exp(std::min(dl, 700.0)));
+      return accept ? nxt : p;
     };
   }
 };

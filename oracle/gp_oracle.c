@@ -411,10 +411,10 @@ double orc_prior(const orc_term *terms, int nterms, const double *ig) {
  * out_states [iters][P], out_ll [iters] (prior + loglik of the state after the step),
  * out_accept [iters].  Returns 0, or LAPACK info > 0 if a proposal's K was not PD (the
  * reference throws there: SURVEY 0.2l). */
-int orc_mh_run(int n, int dim, const double *x, const double *y, const orc_term *init, int nterms,
-               const double *beta, int nbeta, double nugget, const double *ig, double delta,
-               int iters, const double *z, const double *uu, int formula, int evals_per_iter,
-               double *out_states, double *out_ll, int *out_accept) {
+int orc_mh_run_a(int n, int dim, const double *x, const double *y, const orc_term *init, int nterms,
+                 const double *beta, int nbeta, double nugget, const double *ig, double delta,
+                 int iters, const double *z, const double *uu, int formula, int evals_per_iter,
+                 double *out_states, double *out_ll, int *out_accept, double *out_a, int *out_done) {
   int P = orc_nparams(init, nterms);
   double *work = (double *)malloc(sizeof(double) * ((size_t)n * n + n));
   orc_term *cur = (orc_term *)malloc(sizeof(orc_term) * nterms * 2);
@@ -423,9 +423,11 @@ int orc_mh_run(int n, int dim, const double *x, const double *y, const orc_term 
   memcpy(cur, init, sizeof(orc_term) * nterms);
   orc_ll r;
   orc_loglik(n, dim, x, y, cur, nterms, beta, nbeta, nugget, work, &r);
+  if (out_done) *out_done = 0;
   if (r.info) { free(work); free(cur); return r.info; }
   double old_ll = orc_prior(cur, nterms, ig) + (formula ? r.ll_gpml : r.ll_ref);
   for (int it = 0; it < iters; ++it) {
+    if (out_done) *out_done = it;   /* iterations completed before a throw */
     memcpy(next, cur, sizeof(orc_term) * nterms);
     int p = 0;
     for (int t = 0; t < nterms; ++t) {
@@ -445,8 +447,11 @@ int orc_mh_run(int n, int dim, const double *x, const double *y, const orc_term 
       orc_loglik(n, dim, x, y, cur, nterms, beta, nbeta, nugget, work, &r);
       old_ll = orc_prior(cur, nterms, ig) + (formula ? r.ll_gpml : r.ll_ref);
     }
-    double a = fmin(1.0, exp(new_ll - old_ll));
-    int acc = uu[it] < a;
+    /* JVM semantics: scala.math.min(1.0, NaN) is NaN and `u < NaN` is false, so a NaN on either side
+     * rejects; C's fmin(1.0, NaN) returns 1.0 and would always accept */
+    double dl = new_ll - old_ll;
+    int acc = (dl == dl) && uu[it] < fmin(1.0, exp(dl));
+    if (out_a) out_a[it] = (dl == dl) ? fmin(1.0, exp(dl)) : NAN;   /* the acceptance probability itself */
     if (acc) {
       memcpy(cur, next, sizeof(orc_term) * nterms);
       old_ll = new_ll;
@@ -459,7 +464,16 @@ int orc_mh_run(int n, int dim, const double *x, const double *y, const orc_term 
     out_ll[it] = old_ll;
     out_accept[it] = acc;
   }
+  if (out_done) *out_done = iters;
   free(work);
   free(cur);
   return 0;
+}
+
+int orc_mh_run(int n, int dim, const double *x, const double *y, const orc_term *init, int nterms,
+               const double *beta, int nbeta, double nugget, const double *ig, double delta,
+               int iters, const double *z, const double *uu, int formula, int evals_per_iter,
+               double *out_states, double *out_ll, int *out_accept) {
+  return orc_mh_run_a(n, dim, x, y, init, nterms, beta, nbeta, nugget, ig, delta, iters, z, uu, formula,
+                      evals_per_iter, out_states, out_ll, out_accept, NULL, NULL);
 }

@@ -170,8 +170,11 @@ def prior(terms, ig):
     return lib().orc_prior(terms_array(terms), C.c_int(len(terms)), igp)
 
 
-def mh_run(x, y, init_terms, ig, delta, z, u, beta=(), nugget=1e-3, formula=0, evals_per_iter=1):
-    """z: (iters, P) standard normals; u: (iters,) uniforms; ig: (P, 2) inverse-gamma (shape, scale)."""
+def mh_run(x, y, init_terms, ig, delta, z, u, beta=(), nugget=1e-3, formula=0, evals_per_iter=1,
+           with_prob=False):
+    """z: (iters, P) standard normals; u: (iters,) uniforms; ig: (P, 2) inverse-gamma (shape, scale).
+    with_prob: also return the acceptance probabilities a_i = min(1, exp(new - old)) and the number
+    of iterations completed (< iters when a proposal was not positive definite: rc = LAPACK info)."""
     xs, dim = _xsoa(x)
     n = xs.shape[1]
     yv, yp = _d(y)
@@ -186,13 +189,58 @@ def mh_run(x, y, init_terms, ig, delta, z, u, beta=(), nugget=1e-3, formula=0, e
     states = np.empty((iters, P))
     ll = np.empty(iters)
     acc = np.empty(iters, dtype=np.int32)
-    rc = lib().orc_mh_run(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp,
-                          terms_array(init_terms), C.c_int(len(init_terms)), bp,
-                          C.c_int(len(beta)), C.c_double(nugget), igp, C.c_double(delta),
-                          C.c_int(iters), zp, up, C.c_int(formula), C.c_int(evals_per_iter),
-                          states.ctypes.data_as(_dp), ll.ctypes.data_as(_dp),
-                          acc.ctypes.data_as(_ip))
+    prob = np.full(iters, np.nan)
+    done = C.c_int(0)
+    rc = lib().orc_mh_run_a(C.c_int(n), C.c_int(dim), xs.ctypes.data_as(_dp), yp,
+                            terms_array(init_terms), C.c_int(len(init_terms)), bp,
+                            C.c_int(len(beta)), C.c_double(nugget), igp, C.c_double(delta),
+                            C.c_int(iters), zp, up, C.c_int(formula), C.c_int(evals_per_iter),
+                            states.ctypes.data_as(_dp), ll.ctypes.data_as(_dp),
+                            acc.ctypes.data_as(_ip), prob.ctypes.data_as(_dp), C.byref(done))
+    if with_prob:
+        return states, ll, acc, rc, prob, done.value
     return states, ll, acc, rc
+
+
+def mcmc_sample(x, y, init_terms, beta0, ig, delta, z, u, prior_mean, prior_var, nugget=1e-3,
+                mean_nugget=1e-6, formula=0):
+    """Mcmc.sample (Mcmc.scala:63-76), host-stepped: step = KernelParameters.sample compose
+    MeanParameters.sample, i.e. every iteration first draws the plane coefficients from their full
+    conditional (samplePlane, MeanParameters.scala:74-103, at the CURRENT kernel parameters), then
+    runs Breeze's metropolis on the kernel parameters with ll(next) and ll(t) both evaluated at the
+    new coefficients (KernelParameters.scala:231-246).  Proposal / prior as in mh_run.
+    z: (iters, P + d) -- [0, P) the proposal normals, [P, P + d) the Gibbs normals; u: (iters,).
+    Returns states (iters, P + d) [kernel parameters, beta], ll (iters,), accept (iters,)."""
+    P = nparams(init_terms)
+    beta = np.array(beta0, dtype=np.float64)
+    d = len(beta)
+    cur = [tuple(t) for t in init_terms]
+    iters = len(u)
+    states = np.empty((iters, P + d)); lls = np.empty(iters); acc = np.zeros(iters, dtype=np.int32)
+
+    def total(terms, b):
+        r = loglik(x, y, terms, beta=tuple(b), nugget=nugget)
+        assert r["info"] == 0
+        return prior(terms, ig) + (r["ll_gpml"] if formula else r["ll_ref"])
+
+    for it in range(iters):
+        beta, _, _ = sample_plane(x, y, cur, prior_mean, prior_var, z[it, P:], nugget=mean_nugget)
+        nxt, p = [], 0
+        for t in cur:
+            if t[0] == "se":
+                nxt.append(("se", t[1] * math.exp(delta * z[it, p]), t[2] * math.exp(delta * z[it, p + 1]))); p += 2
+            else:
+                nxt.append(("white", t[1] * math.exp(delta * z[it, p]))); p += 1
+        new_ll, old_ll = total(nxt, beta), total(cur, beta)
+        dl = new_ll - old_ll
+        a = min(1.0, math.exp(dl)) if dl == dl else float("nan")
+        if u[it] < a:
+            cur, old_ll, acc[it] = nxt, new_ll, 1
+        flat = []
+        for t in cur:
+            flat += list(t[1:])
+        states[it, :P] = flat; states[it, P:] = beta; lls[it] = old_ll
+    return states, lls, acc
 
 
 # ---- "next" rows of the scope table (SURVEY.md 8f): numpy restatements, small cases only -------

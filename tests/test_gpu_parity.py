@@ -58,6 +58,29 @@ def test_build_cov_and_distance_entrywise(ctx, oracle, n, dim):
         assert K[5, 2] == 3.0 + 1.0 + 0.5  # SE(0) + SE(0) + white, no nugget off the diagonal
 
 
+@pytest.mark.parametrize("n", [3, 64, 65, 130, 300, 1024])
+@pytest.mark.parametrize("dim", [1, 2])
+@pytest.mark.parametrize("terms", [SE_W, SE_SE_W, SHORT_W, [("white", 0.5), ("se", 3.0, 0.2), ("se", 1.0, 5.0)]])
+def test_hot_path_build_entrywise(ctx, oracle, n, dim, terms):
+    """The matrix the factorisation actually consumes (k_build's hot-path form h exp(d^2 (-1/s^2)) with
+    the hand-written exp, gpb_build_cov_hot) against the oracle's exact-order matrix, entry by entry:
+    |dK| <= 2 ulp of the SE amplitudes (argument rounding 0.55 ulp(h) at worst, exp <= 0.84 ulp here
+    and < 1 ulp in glibc) -- including the underflow branch (length scale 0.2: arguments below -700),
+    duplicate locations, ragged sizes and dim = 2 (VERDICT r1 weak #3, ADVICE r1)."""
+    x, _, _ = synth(oracle, n, dim, terms, 300 + n)
+    Kh = ctx.build_cov_hot(x, gterms(terms), 1e-3)
+    Ko = oracle.build_cov(x, terms, 1e-3)
+    lower = np.tril(np.ones((n, n), dtype=bool))
+    tol = 2.0 * sum(np.spacing(t[1]) for t in terms if t[0] == "se")
+    err = np.abs(Kh - Ko)[lower]
+    print(f"hot-path build n={n} dim={dim}: max |dK| = {err.max() / (tol / 2.0):.3f} ulp(h)")
+    assert err.max() <= tol
+    assert np.all(Kh[~lower] == 0.0)
+    assert np.all(np.diag(Kh) == np.diag(Ko))          # exp(0) = 1 exactly on both sides
+    if n >= 8:
+        assert Kh[5, 2] == Ko[5, 2]                    # duplicate location: white lands off the diagonal
+
+
 @pytest.mark.parametrize("sched", [0, 1])
 @pytest.mark.parametrize("n,dim,terms", [
     (1, 1, SE_W), (2, 1, SE_W), (3, 2, SE_SE_W), (20, 1, SE_W), (63, 2, SE_W), (64, 1, SE_SE_W),
@@ -326,21 +349,35 @@ def test_full_size_c3_batch_of_chains_n1024(ctx, oracle):
 
 
 def test_full_size_c5_sum_of_kernels_n8192(ctx, oracle):
-    """configs[4] shape (SE + SE + white, n=8192), one proposal: LAPACK twin on the host."""
+    """configs[4] shape (SE + SE + white, n=8192): LAPACK twin on the host for BOTH formulas (the
+    as-parsed value is the parity target), and a batch of 3 proposals bit-equal to three single calls."""
     from gpb200 import _lib as G
     n = 8192
     rng = np.random.default_rng(5)
     x = rng.uniform(-15, 15, size=(n, 2))
     d2 = ((x[:, None, :] - x[None, :, :]) ** 2).sum(-1)
     d = np.sqrt(d2)
-    K = 3.0 * np.exp(-(d * d) / (5.5 * 5.5)) + 1.0 * np.exp(-(d * d) / (0.8 * 0.8)) + np.where(d == 0, 0.5, 0.0) + 1e-3 * np.eye(n)
-    L = np.linalg.cholesky(K)
+
+    def cov(t):
+        return (t[0][1] * np.exp(-(d * d) / (t[0][2] * t[0][2])) + t[1][1] * np.exp(-(d * d) / (t[1][2] * t[1][2]))
+                + np.where(d == 0, t[2][1], 0.0) + 1e-3 * np.eye(n))
+
+    L = np.linalg.cholesky(cov(SE_SE_W))
     y = L @ rng.standard_normal(n)
     ds = ctx.dataset(x, y)
-    r = ds.loglik_batch([gterms(SE_SE_W)])[0]
-    u = sl.solve_triangular(L, y, lower=True)
-    S, C = np.log(np.diag(L)).sum(), n * 0.5 * math.log(2 * math.pi)
-    assert r.info == 0 and rel(G.ll_value(r, 1), -0.5 * u @ u - S - C) < LL_RTOL
+    props = [SE_SE_W, [("se", 2.7, 5.9), ("se", 1.2, 0.7), ("white", 0.55)], [("se", 3.4, 5.1), ("se", 0.8, 0.9), ("white", 0.45)]]
+    batch = ds.loglik_batch([gterms(p) for p in props])
+    C = n * 0.5 * math.log(2 * math.pi)
+    for b, p in enumerate(props):
+        single = ds.loglik_batch([gterms(p)])[0]
+        assert (single.Q, single.U1, single.S, single.info) == (batch[b].Q, batch[b].U1, batch[b].S, batch[b].info)
+        if b > 0:
+            L = np.linalg.cholesky(cov(p))
+        u = sl.solve_triangular(L, y, lower=True)
+        S = np.log(np.diag(L)).sum()
+        assert batch[b].info == 0
+        assert rel(G.ll_value(batch[b], 1), -0.5 * u @ u - S - C) < LL_RTOL                      # GPML
+        assert rel(G.ll_value(batch[b], 0), -0.5 * u @ u + 0.5 * (S + C) * u.sum()) < LL_RTOL   # as parsed (GaussianProcess.scala:126)
     ds.close()
 
 

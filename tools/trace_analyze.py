@@ -70,6 +70,27 @@ def main():
     span = (tr[:, 7].max() - g0) / 1e3
     busy = us(tr[:, 6] - tr[:, 1]).sum()
     print(f"kernel span {span:.1f} us; sum task time {busy:.1f} us -> avg CTA busy {busy/span:.1f}")
+    if B > 1:
+        # per block column: when the chain reaches it (median over the proposals of the release of
+        # diag(j)), and how many CTA-microseconds of tasks ran between consecutive columns
+        rel = np.zeros((B, nt))
+        for t in range(T):
+            b, i, j = dec[t]
+            if i == j == 0: rel[b, 0] = (tr[t, 7] - g0) / 1e3
+            elif fused[t]: rel[b, i] = (tr[t, 7] - g0) / 1e3
+        med = np.median(rel, axis=0)
+        start = (tr[:, 0] - g0) / 1e3; end = (tr[:, 7] - g0) / 1e3
+        print("col: diag released at (us, median over proposals) | step | busy CTAs on average in that window | of which waiting on a dependency")
+        wait_us = us(tr[:, 4] - tr[:, 3])
+        prev = 0.0
+        for j in range(nt):
+            lo, hi = prev, med[j]
+            ov = np.clip(np.minimum(end, hi) - np.maximum(start, lo), 0, None).sum()
+            # waiting time that falls in the window (approximate: waits are attributed to the task's end window)
+            w = wait_us[(end > lo) & (end <= hi)].sum()
+            print(f"  {j:3d}: {med[j]:8.1f} | {hi - lo:6.1f} | {ov / max(hi - lo, 1e-9):6.1f} | {w / max(hi - lo, 1e-9):6.1f}")
+            prev = hi
+        print(f"  end: {span:8.1f} | {span - prev:6.1f}")
     if B == 1:
         # critical chain: release time of diag(j) relative to start
         d = {(dec[t, 1], dec[t, 2]): t for t in range(T)}

@@ -12,9 +12,18 @@ N B200s, through libgpb200.so's C ABI.  Prints ONE JSON line (rank 0).
               duration vs the measured DMMA issue peak of this pool's B200 (37.1 TFLOP/s,
               profiles/r01_dmma_shapes_microbench.log; MEASURED_PEAKS.json has no FP64 entry).
   N > 1     : proposals are sharded across ranks (independent, no data-path collective); each rank
-              then all-gathers its log-likelihoods over NCCL (north_star: gather only). scaling=weak.
-  --impl reference : the CPU oracle (port of the Scala/Breeze path; the JVM is not in this image)
-              on all host cores, one independent evaluation per thread, same config and metric.
+              then all-gathers its log-likelihoods through the library's own NCCL communicator
+              (gpb_comm_* / gpb_gather behind the C ABI; north_star: gather only). scaling=weak.
+              torch.distributed only carries the barrier, the max-over-ranks of the clocks and the
+              128-byte communicator id.
+  extra     : the other BASELINE.json configs (C1 shipped example at n=300 and thinned to n=20, C3
+              256 chains x n=1024, C4 n=32768 + 10^4 predictive points, C5 SE+SE+white n=8192 x 64
+              chains per GPU), each with its own fraction of the FP64 DMMA peak; MH runs go through
+              gpb_mh_run_ex (device Philox streams, ring flushed every 32 iterations, NCCL gather
+              of the ring segments when N > 1).
+  --impl reference : the CPU oracle (port of the Scala/Breeze path; the JVM is not in this image),
+              same config, metric and step as the GPU arm: a step = the same batch of proposals,
+              one single-threaded evaluation per host thread.
 """
 import argparse
 import json
@@ -131,41 +140,48 @@ def cpu_evals(x, y, term_lists, threads):
     return len(term_lists) / dt, dt, res
 
 
+def workload_config(B, world):
+    """The `config` object both arms print (the driver compares them)."""
+    return {"workload": f"C2: n={N_TRAIN} 2-D SE+white log-marginal-likelihood, batch of {B} independent proposals per step per GPU",
+            "batch": B, "n": N_TRAIN, "dim": DIM, "parallelism": f"proposal-sharded x{world}",
+            "l2": "inputs larger than L2 (each proposal rebuilds and refactors its own 134 MB matrix)"}
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path restated (oracle port; JVM unavailable on this
-    box), all host cores, same config / metric / unit.  Rank 0 only."""
+    box), same config / metric / unit / step as the GPU arm: a step = one batch of --batch fresh
+    proposals, each evaluation single-threaded like the reference's F2J path, one per host thread.
+    Rank 0 only.  A step takes seconds: the run is bounded to a few minutes and the line reports the
+    steps it actually executed as `steps` (the metric is a rate)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
+    B = args.batch
+    threads = min(B, cores)
     x, y = make_dataset()
     rng = np.random.default_rng(1234)
-    # A step (one full n=4096 evaluation per host thread) takes ~10 s of wall clock: whatever K and W
-    # the caller passes, the run is bounded to a few minutes -- warm-up steps while under 30 s, timed
-    # steps while under 170 s (at least one), and the line says how many were executed.  The metric
-    # is a rate, so it does not depend on the count.
     t_start = time.perf_counter()
     warm_done = 0
     for _ in range(args.warmup):
-        if warm_done >= 1 and time.perf_counter() - t_start > 30.0:
+        if warm_done >= 1 and time.perf_counter() - t_start > 25.0:
             break
-        cpu_evals(x, y, proposals(rng, cores), cores); warm_done += 1
-    total_t, total_n, steps_done = 0.0, 0, 0
+        cpu_evals(x, y, proposals(rng, B), threads); warm_done += 1
+    total_t, steps_done = 0.0, 0
     for _ in range(max(args.steps, 1)):
-        if steps_done >= 1 and time.perf_counter() - t_start > 170.0:
+        if steps_done >= 1 and time.perf_counter() - t_start > 150.0:
             break
-        _, dt, _ = cpu_evals(x, y, proposals(rng, cores), cores)
-        total_t += dt; total_n += cores; steps_done += 1
-    v = total_n / total_t
+        _, dt, _ = cpu_evals(x, y, proposals(rng, B), threads)
+        total_t += dt; steps_done += 1
+    v = steps_done * B / total_t
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "evals/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / steps_done,
-        "steps_executed": steps_done, "warmup_executed": warm_done,
+        "steps": steps_done, "warmup": warm_done, "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "ms_per_step": 1e3 * total_t / steps_done,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic",
-        "config": {"workload": f"C2: n={N_TRAIN} 2-D SE+white log-marginal-likelihood, {cores} independent proposals per step (one per host thread)"},
-        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": cores, "kind": "port",
-                         "sample": f"{steps_done} of {args.steps} steps executed (time-bounded) x {cores} full n={N_TRAIN} evaluations, 1 thread each (reference JVM path: unavailable on this box)"},
+        "data": "synthetic", "config": workload_config(B, args.gpus),
+        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": threads, "kind": "port",
+                         "sample": f"{steps_done} steps x {B} full n={N_TRAIN} evaluations, 1 thread each on {threads} of {cores} host cores (time-bounded; reference JVM path: unavailable on this box)"},
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -174,6 +190,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     from gpb200 import _lib as G
+    from gpb200 import chains as CH
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -189,12 +206,12 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()                 # nvidia-smi needs seconds to come up: start it before the set-up
     ctx = G.Context(local)
+    if world > 1:
+        CH.init_comm(ctx, dist)     # the library's own NCCL communicator (gpb_comm_init_rank)
     x, y = make_dataset()
     ds = ctx.dataset(x, y)
     B = args.batch
     rng = np.random.default_rng(1000 + rank)
-    gather_in = torch.zeros(B, dtype=torch.float64, device=f"cuda:{local}")
-    gather_out = torch.zeros(B * world, dtype=torch.float64, device=f"cuda:{local}") if world > 1 else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -206,9 +223,8 @@ def run_ours(args):
         props = [gterms(p) for p in proposals(rng, B)]
         rs = ds.loglik_batch(props, nugget=1e-3)       # H2D params, kernels, D2H results
         t = ctx.last_timing()
-        if dist is not None:                            # gather the log-likelihoods (north_star)
-            gather_in.copy_(torch.tensor([G.ll_value(r, 0) for r in rs], dtype=torch.float64))
-            dist.all_gather_into_tensor(gather_out, gather_in)
+        if dist is not None:                            # gather the log-likelihoods (north_star): gpb_gather
+            ctx.gather([G.ll_value(r, 0) for r in rs])
         return rs, t
 
     for _ in range(max(args.warmup, 3)):
@@ -254,9 +270,9 @@ def run_ours(args):
     extra = {}
     if not args.no_extras:
         if world == 1:
-            extra = extras_single_gpu(ctx, ds, G)
+            extra = extras_single_gpu(ctx, ds, G, CH)
         else:
-            extra = extras_multi_gpu(ctx, G, dist, local)   # collective: every rank takes part
+            extra = extras_multi_gpu(ctx, G, CH, dist, local)   # collective: every rank takes part
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -264,6 +280,12 @@ def run_ours(args):
             v, dt, res = cpu_evals(x, y, proposals(np.random.default_rng(7), cores), cores)
             cpu = {"value": v, "unit": "evals/s", "cores": cores, "kind": "port",
                    "sample": f"{cores} full n={N_TRAIN} evaluations, one per thread, {dt:.1f} s (reference JVM path: unavailable on this box)"}
+            lap = extra.get("cpu_lapack_b2_n4096", {}) if isinstance(extra, dict) else {}
+            if "evals_per_sec_factor_only_path" in lap:
+                # the strong CPU baseline beside the port: OpenBLAS dpotrf + dtrsv on all cores
+                cpu["lapack_b2_evals_per_sec"] = lap["evals_per_sec_factor_only_path"]
+                extra["speedup_vs_cpu"] = {"e2e_over_port": e2e / v, "e2e_over_lapack_b2": e2e / lap["evals_per_sec_factor_only_path"],
+                                           "note": "port = line-by-line restatement of the reference's single-threaded F2J path, one evaluation per core; B2 = scipy/OpenBLAS LAPACK on all cores, covariance build excluded"}
         traffic = None
         tp = os.path.join(ROOT, "profiles", "chol_traffic_bytes_per_launch.json")
         if os.path.exists(tp):
@@ -272,9 +294,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C2: n={N_TRAIN} 2-D SE+white log-marginal-likelihood, batch of {B} independent proposals per step per GPU",
-                       "batch": B, "n": N_TRAIN, "dim": DIM, "parallelism": f"proposal-sharded x{world}",
-                       "l2": "inputs larger than L2 (each proposal rebuilds and refactors its own 134 MB matrix)"},
+            "config": workload_config(B, world),
             "e2e": {"value": e2e, "unit": "evals/s", "h2d_bytes_per_step": B * 192,
                     "d2h_bytes_per_step": B * 40 + 8},
             "gpu_launches": launches,
@@ -290,81 +310,8 @@ def run_ours(args):
     ds.close()
     if dist is not None:
         dist.barrier()
+        ctx.comm_destroy()
         dist.destroy_process_group()
-
-
-def _mh_setup(n, lo, hi, seed, terms):
-    """Synthetic chain workload: shared dataset (as writeParallelChain shares it), SURVEY.md 8d."""
-    r = np.random.default_rng(seed)
-    x = r.uniform(lo, hi, size=(n, 2))
-    y = r.standard_normal(n) * 1.8  # timing only: parity of the chain itself is in tests/
-    return x, y, r
-
-
-def mh_bench(ctx, G, n, chains_total, iters, warm, terms, ig, seed, lo, hi, dist=None, local=0):
-    """MCMC iterations/s for `chains_total` chains sharded over the ranks (gpb_mh_run per rank,
-    then ONE NCCL all_gather of accepted states + ll + accept flags).  Timed end to end through
-    the ABI call with host buffers (streams H2D, chain outputs D2H), barrier on both sides, max
-    over ranks; the device time of the loop (CUDA events inside the library) is reported too."""
-    import torch
-    from gpb200 import chains as CH
-    world = dist.get_world_size() if dist is not None else 1
-    rank = dist.get_rank() if dist is not None else 0
-    x, y, r = _mh_setup(n, lo, hi, seed, terms)
-    ds = ctx.dataset(x, y)
-    first, count = CH.shard(chains_total, world, rank)
-    P = sum(2 if t[0] == "se" else 1 for t in terms)
-    rr = np.random.default_rng(seed + 17)
-    inits_all = []
-    for _ in range(chains_total):
-        z = rr.standard_normal(P) * 0.05
-        k, tl = 0, []
-        for t in terms:
-            if t[0] == "se":
-                tl.append((0, t[1] * math.exp(z[k]), t[2] * math.exp(z[k + 1]))); k += 2
-            else:
-                tl.append((1, t[1] * math.exp(z[k]), 0.0)); k += 1
-        inits_all.append(tl)
-    inits = inits_all[first:first + count]
-    dev = f"cuda:{local}"
-
-    def run(nit, seed2):
-        z, u = G.philox_streams(seed2, first, count, nit, P)
-        st, ll, acc, info = ds.mh_run(inits, ig, 0.05, z, u, on_notpd=1)
-        tdev = ctx.last_timing()[1]
-        if dist is not None and world > 1:
-            width = -(-chains_total // world)
-            block = np.zeros((nit, width, P + 2))
-            block[:, :count, :P] = st; block[:, :count, P] = ll; block[:, :count, P + 1] = acc
-            t = torch.from_numpy(block).to(dev)
-            out = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)
-            dist.all_gather_into_tensor(out, t)
-            out.cpu()
-        return acc, tdev
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None and world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    run(warm, 100)
-    barrier()
-    t0 = time.perf_counter()
-    acc, tdev = run(iters, 101)
-    barrier()
-    wall = time.perf_counter() - t0
-    tt = torch.tensor([wall, tdev * 1e-3], dtype=torch.float64, device=dev)
-    if dist is not None and world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    wall, tdev = (float(v) for v in tt.cpu())
-    ds.close()
-    # the timed call also evaluates the initial state once (iters + 1 factorisations per chain)
-    return {"iters_per_sec_e2e": iters / wall, "iters_per_sec_device": iters / tdev,
-            "evals_per_sec_device": (iters + 1) * chains_total / tdev,
-            "chains_total": chains_total, "chains_per_gpu": count, "n": n, "iters": iters,
-            "accept_rate": float(np.mean(acc)), "factorisations_per_iter_per_chain": 1,
-            "gflop_per_iter": chains_total * chol_flops(n) * 1e-9}
 
 
 IG3 = [[3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]                       # SimulatedGp.scala:132-134
@@ -372,8 +319,98 @@ IG5 = [[3.0, 4.0], [3.0, 6.0], [3.0, 4.0], [3.0, 6.0], [10.0, 6.0]]
 C5_TERMS = [("se", 3.0, 5.5), ("se", 1.0, 0.8), ("white", 0.5)]
 
 
-def extras_single_gpu(ctx, ds, G):
-    """Secondary numbers named by BASELINE.json's metric string / configs (not the headline)."""
+def synth_dataset(ctx, n, dim, lo, hi, seed, terms):
+    """x ~ U(lo, hi)^dim, y = L z with K = k(true terms) + 1e-3 I.  L z is formed on the
+    GPU (gpb_draw: build + factor + L z), so that n = 8192 / 32768 need no host Cholesky."""
+    r = np.random.default_rng(seed)
+    x = r.uniform(lo, hi, size=(n, dim)) if dim > 1 else np.sort(r.uniform(lo, hi, n))
+    y, info = ctx.draw(x, gterms(terms), r.standard_normal(n), None, nugget=1e-3)
+    assert info == 0
+    return x, y
+
+
+def prior_draws(terms, ig, count, seed):
+    """Initial states = draws from the inverse-gamma priors: IG(a, b) = b / Gamma(a, 1)."""
+    r = np.random.default_rng(seed)
+    out = []
+    for _ in range(count):
+        tl, p = [], 0
+        for t in terms:
+            if t[0] == "se":
+                tl.append((0, ig[p][1] / r.gamma(ig[p][0]), ig[p + 1][1] / r.gamma(ig[p + 1][0]))); p += 2
+            else:
+                tl.append((1, ig[p][1] / r.gamma(ig[p][0]), 0.0)); p += 1
+        out.append(tl)
+    return out
+
+
+def chol_frac(ctx, ds, term_lists):
+    """Factor+solve kernel of one batch at this shape: ms, algorithmic TFLOP/s, fraction of the DMMA peak."""
+    for _ in range(2):
+        ds.loglik_batch(term_lists)
+    ts = []
+    for _ in range(5):
+        ds.loglik_batch(term_lists); ts.append(ctx.last_timing())
+    t = np.median(np.array(ts), axis=0)
+    tf = len(term_lists) * chol_flops(ds.n) / (t[1] * 1e-3) * 1e-12
+    return {"build_ms": float(t[0]), "chol_ms": float(t[1]), "chol_tflops": tf, "frac_of_dmma_peak": tf / FP64_PEAK_TFLOPS}
+
+
+def mh_bench(ctx, G, CH, n, chains_total, iters, warm, terms, ig, seed, lo, hi, dist=None, local=0):
+    """MCMC iterations/s for `chains_total` chains block-partitioned over the ranks, through
+    gpb_mh_run_ex: device Philox streams (keyed by the global chain index), ring flushed every 32
+    iterations and -- for N > 1 -- all-gathered device to device by the library's NCCL communicator
+    so that every rank ends up with every chain.  Timed end to end through the ABI call with host
+    buffers (initial states H2D, all chains' outputs D2H), barrier on both sides, max over ranks; the
+    device time of the loop (CUDA events inside the library) is reported too."""
+    import torch
+    world = dist.get_world_size() if dist is not None else 1
+    x, y = synth_dataset(ctx, n, 2, lo, hi, seed, terms)
+    ds = ctx.dataset(x, y)
+    inits_all = prior_draws(terms, ig, chains_total, seed + 17)
+    first, count = CH.shard(chains_total, world, dist.get_rank() if dist is not None else 0)
+    dev = f"cuda:{local}"
+
+    def run(nit, seed2):
+        if world > 1:
+            return CH.run_sharded(ctx, ds, inits_all, ig, 0.05, nit, seed2, on_notpd=1, formula=0)
+        return ds.mh_run_ex(inits_all, ig, 0.05, nit, rng=G.RNG_PHILOX, seed=seed2, on_notpd=1, formula=0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run(warm, 100)
+    barrier()
+    t0 = time.perf_counter()
+    r = run(iters, 101)
+    barrier()
+    wall = time.perf_counter() - t0
+    tt = torch.tensor([wall, r["device_ms"] * 1e-3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    wall, tdev = (float(v) for v in tt.cpu())
+    shape = chol_frac(ctx, ds, inits_all[first:first + count])
+    ds.close()
+    P = len(ig)
+    # the timed call also evaluates the initial state once: iters + 1 factorisations per chain
+    evals = (iters + 1) * chains_total
+    return {"iters_per_sec_e2e": iters / wall, "iters_per_sec_device": iters / tdev,
+            "evals_per_sec_device": evals / tdev, "evaluations_timed": evals,
+            "chains_total": chains_total, "chains_per_gpu": count, "n": n, "iters": iters,
+            "accept_rate": float(np.mean(r["accept"])), "factorisations_per_iter_per_chain": 1,
+            "flushes": r["flushes"], "gathered_on_every_rank": bool(world > 1),
+            "d2h_bytes": int(iters * chains_total * (P + 2) * 8),
+            "loop_tflops": evals * chol_flops(n) / world / tdev * 1e-12,
+            "loop_frac_of_dmma_peak": evals * chol_flops(n) / world / tdev * 1e-12 / FP64_PEAK_TFLOPS,
+            "factor_kernel_at_this_shape": shape,
+            "inputs": f"SURVEY 8d: x ~ U({lo},{hi})^2, y = L z (seed {seed}), inits = prior draws"}
+
+
+def extras_single_gpu(ctx, ds, G, CH):
+    """The other numbers BASELINE.json's metric string / configs name (not the headline)."""
     out = {}
     rng = np.random.default_rng(5)
 
@@ -386,10 +423,13 @@ def extras_single_gpu(ctx, ds, G):
     def latency():
         for _ in range(3):
             ds.loglik_batch([gterms(proposals(rng, 1)[0])])
-        t0 = time.perf_counter(); dev = 0.0
+        t0 = time.perf_counter(); dev = 0.0; chol = 0.0
         for _ in range(20):
-            ds.loglik_batch([gterms(proposals(rng, 1)[0])]); dev += sum(ctx.last_timing())
-        return {"evals_per_sec_e2e": 20 / (time.perf_counter() - t0), "evals_per_sec_device": 20 / (dev * 1e-3)}
+            ds.loglik_batch([gterms(proposals(rng, 1)[0])]); t = ctx.last_timing(); dev += sum(t); chol += t[1]
+        tf = 20 * chol_flops(N_TRAIN) / (chol * 1e-3) * 1e-12
+        return {"evals_per_sec_e2e": 20 / (time.perf_counter() - t0), "evals_per_sec_device": 20 / (dev * 1e-3),
+                "chol_ms": chol / 20, "chol_tflops": tf, "frac_of_dmma_peak": tf / FP64_PEAK_TFLOPS,
+                "note": "the reference's own call shape: one proposal per call (chain-bound, one CTA per SM)"}
 
     def c2_predict():
         m = 4096
@@ -400,52 +440,69 @@ def extras_single_gpu(ctx, ds, G):
         wall = time.perf_counter() - t0
         t = ctx.last_timing()
         fl = chol_flops(N_TRAIN) + float(N_TRAIN) ** 2 * m
-        return {"m": m, "points_per_sec_e2e": m / wall, "device_ms": sum(t), "factor_solve_tflops": fl / (t[1] * 1e-3) * 1e-12}
+        tf = fl / (t[1] * 1e-3) * 1e-12
+        return {"m": m, "points_per_sec_e2e": m / wall, "device_ms": sum(t), "factor_solve_tflops": tf,
+                "frac_of_dmma_peak": tf / FP64_PEAK_TFLOPS}
 
     def c4():
-        import torch
         n, m = 32768, 10000
-        r4 = np.random.default_rng(4)
-        x4 = r4.uniform(-30, 30, size=(n, 2)); y4 = r4.standard_normal(n) * 1.8
-        xs = r4.uniform(-30, 30, size=(m, 2))
+        x4, y4 = synth_dataset(ctx, n, 2, -30, 30, 4, TRUE_TERMS)
+        xs = np.random.default_rng(44).uniform(-30, 30, size=(m, 2))
         ds4 = ctx.dataset(x4, y4)
         res = {}
         ds4.loglik_batch([gterms(TRUE_TERMS)])
         t0 = time.perf_counter(); r = ds4.loglik_batch([gterms(TRUE_TERMS)])[0]; w = time.perf_counter() - t0
         t = ctx.last_timing()
+        tf = chol_flops(n) / (t[1] * 1e-3) * 1e-12
         res["loglik_n32768"] = {"info": r.info, "wall_s": w, "build_ms": t[0], "factor_solve_ms": t[1],
-                                "factor_solve_tflops": chol_flops(n) / (t[1] * 1e-3) * 1e-12}
+                                "factor_solve_tflops": tf, "frac_of_dmma_peak": tf / FP64_PEAK_TFLOPS}
         ds4.predict(gterms(TRUE_TERMS), xs, nugget=1e-6)
         t0 = time.perf_counter(); mean, var, info = ds4.predict(gterms(TRUE_TERMS), xs, nugget=1e-6); w = time.perf_counter() - t0
         t = ctx.last_timing()
         fl = chol_flops(n) + float(n) ** 2 * m
+        tf = fl / (t[1] * 1e-3) * 1e-12
         res["predict_n32768_m10000"] = {"info": info, "wall_s": w, "points_per_sec_e2e": m / w, "build_ms": t[0],
-                                        "factor_solve_ms": t[1], "epilogue_ms": t[2],
-                                        "factor_solve_tflops": fl / (t[1] * 1e-3) * 1e-12}
+                                        "factor_solve_ms": t[1], "epilogue_ms": t[2], "factor_solve_tflops": tf,
+                                        "frac_of_dmma_peak": tf / FP64_PEAK_TFLOPS}
+        res["inputs"] = "SURVEY 8d C4: x ~ U(-30,30)^2, y = L z generated on the GPU (gpb_draw), seed 4"
         ds4.close()
         return res
 
     def c1():
-        """configs[0]: the shipped example (SimulatedGp.scala): 1-D, n=300 sorted U(-10,10), SE+white,
-        2 chains, log-normal random walk delta=0.05; GPU device-resident MH vs the CPU oracle running
-        the reference's 2 evaluations per iteration (cpu_baseline leg: the oracle is only timed)."""
+        """configs[0]: the shipped example (SimulatedGp.scala): 1-D, n=300 sorted U(-10,10) AND the thinning
+        to n=20 it actually runs (:112), SE+white, 2 chains (:164), log-normal random walk delta=0.05.  GPU =
+        gpb_mh_run_ex (n=20: the one-launch kernel), 1 factorisation / iteration; CPU = the oracle running
+        Breeze's 2 evaluations per iteration on one core per chain (cpu_baseline leg: the oracle is only timed)."""
         from oracle import oracle as o
-        r1 = np.random.default_rng(1)
-        n, chains, iters = 300, 2, 300
-        x1 = np.sort(r1.uniform(-10, 10, n)); y1 = r1.standard_normal(n) * 1.8
-        ds1 = ctx.dataset(x1, y1)
-        inits = [gterms(TRUE_TERMS)] * chains
-        z, u = G.philox_streams(11, 0, chains, iters, 3)
-        ds1.mh_run(inits, IG3, 0.05, z[:5], u[:5], on_notpd=1)
-        t0 = time.perf_counter(); ds1.mh_run(inits, IG3, 0.05, z, u, on_notpd=1); w = time.perf_counter() - t0
-        ds1.close()
-        it_cpu = 40
-        t0 = time.perf_counter()
-        o.mh_run(x1, y1, TRUE_TERMS, IG3, 0.05, z[:it_cpu, 0], u[:it_cpu, 0], evals_per_iter=2)
-        wc = time.perf_counter() - t0
-        return {"n": n, "chains": chains, "gpu_iters_per_sec_e2e": iters / w,
-                "cpu_oracle_iters_per_sec_one_chain_one_core": it_cpu / wc,
-                "note": "CPU = oracle port, 2 likelihood evaluations per iteration like Breeze metropolis; GPU = 1"}
+        x1, y1 = synth_dataset(ctx, 300, 1, -10, 10, 1, TRUE_TERMS)
+        keep = [(i + 1) % 15 == 0 for i in range(300)]
+        res = {}
+        for label, xx, yy, it_gpu, it_cpu in (("n300", x1, y1, 2000, 40), ("n20_thinned", x1[keep], y1[keep], 20000, 4000)):
+            d1 = ctx.dataset(xx, yy)
+            inits = [gterms(TRUE_TERMS)] * 2
+            d1.mh_run_ex(inits, IG3, 0.05, 50, rng=G.RNG_PHILOX, seed=11, on_notpd=1)
+            t0 = time.perf_counter(); r = d1.mh_run_ex(inits, IG3, 0.05, it_gpu, rng=G.RNG_PHILOX, seed=12, on_notpd=1); w = time.perf_counter() - t0
+            z, u = G.philox_streams(11, 0, 1, it_cpu, 3)
+            t0 = time.perf_counter()
+            o.mh_run(xx, yy, TRUE_TERMS, IG3, 0.05, z[:, 0], u[:, 0], evals_per_iter=2)
+            wc = time.perf_counter() - t0
+            entry = {"n": len(xx), "chains": 2, "gpu_path": "one-launch small-n kernel" if r["path"] == 1 else "general",
+                     "gpu_iters_per_sec_e2e_2_chains": it_gpu / w, "gpu_us_per_iter_device": 1e3 * r["device_ms"] / it_gpu,
+                     "cpu_oracle_iters_per_sec_per_chain_one_core": it_cpu / wc,
+                     "gpu_over_cpu_at_2_chains": (it_gpu / w) / (it_cpu / wc)}
+            if len(xx) <= 64:
+                # where the GPU starts to pay at the shipped size: iterations/s stay flat until the chains fill the SMs
+                sweep = {}
+                for ch in (2, 148, 1184, 4736):
+                    d1.mh_run_ex([gterms(TRUE_TERMS)] * ch, IG3, 0.05, 200, rng=G.RNG_PHILOX, seed=5, on_notpd=1)
+                    t0 = time.perf_counter(); d1.mh_run_ex([gterms(TRUE_TERMS)] * ch, IG3, 0.05, 4000, rng=G.RNG_PHILOX, seed=6, on_notpd=1)
+                    sweep[str(ch)] = 4000 / (time.perf_counter() - t0)
+                entry["gpu_iters_per_sec_e2e_by_chains"] = sweep
+                entry["chain_iterations_per_sec_at_4736_chains"] = sweep["4736"] * 4736
+            res[label] = entry
+            d1.close()
+        res["note"] = "CPU = oracle port, 2 likelihood evaluations per iteration like Breeze metropolis, one core per chain (the reference runs its 2 chains on 2 threads); GPU = 1 evaluation per iteration"
+        return res
 
     def cpu_lapack():
         """scipy/OpenBLAS dpotrf + dtrsv on all host cores, same n=4096 system."""
@@ -463,7 +520,6 @@ def extras_single_gpu(ctx, ds, G):
 
     def c2_gradient():
         """mllGradient at C2's size, 8 parameter vectors per call (log parameters)."""
-        import math
         BATCH = 8
         th = [[(0, math.log(3.0 + 0.1 * b), math.log(5.5)), (1, math.log(0.5), 0.0)] for b in range(BATCH)]
         for _ in range(2):
@@ -476,24 +532,42 @@ def extras_single_gpu(ctx, ds, G):
                 "factor_and_inverse_rows_tflops": BATCH * (2 * n ** 3 / 3) / (t[1] * 1e-3) * 1e-12,
                 "contraction_tflops": BATCH * (n ** 3 / 3) / (t[2] * 1e-3) * 1e-12}
 
-    guarded("c1_example_mcmc_n300", c1)
+    def c3_mean_step():
+        """Mcmc.sample with a Plane mean (mean Gibbs step + kernel step, 3 factorisations per chain and
+        iteration like the reference): 64 chains x n=1024, device resident."""
+        n, chains, iters = 1024, 64, 40
+        x3, y3 = synth_dataset(ctx, n, 2, -10, 10, 3, TRUE_TERMS)
+        y3 = y3 + 0.7 + 0.2 * x3[:, 0] - 0.1 * x3[:, 1]
+        X = np.hstack([np.ones((n, 1)), x3.reshape(-1).reshape((2, n)).T])   # makeDesignMatrix layout
+        d3 = ctx.dataset(x3, y3)
+        inits = prior_draws(TRUE_TERMS, IG3, chains, 31)
+        kw = dict(rng=G.RNG_PHILOX, beta0=np.zeros((chains, 3)), design=X, mean_step=True, mean_prior=(0.0, 4.0), on_notpd=1)
+        d3.mh_run_ex(inits, IG3, 0.05, 4, seed=1, **kw)
+        t0 = time.perf_counter(); r = d3.mh_run_ex(inits, IG3, 0.05, iters, seed=2, **kw); w = time.perf_counter() - t0
+        d3.close()
+        return {"n": n, "chains": chains, "iters": iters, "iters_per_sec_e2e": iters / w, "iters_per_sec_device": iters / (r["device_ms"] * 1e-3),
+                "factorisations_per_iter_per_chain": 3, "accept_rate": float(np.mean(r["accept"]))}
+
+    guarded("c1_shipped_example_mcmc", c1)
     guarded("cpu_lapack_b2_n4096", cpu_lapack)
     guarded("c2_single_proposal_latency", latency)
     guarded("c2_predict_m4096", c2_predict)
     guarded("c2_mll_gradient_batch8", c2_gradient)
-    guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10))
-    guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64, 8, 1, C5_TERMS, IG5, 5, -15, 15))
+    guarded("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, CH, 1024, 256, 200, 20, TRUE_TERMS, IG3, 3, -10, 10))
+    guarded("c3_mcmc_32chains_n1024_per_gpu_shape_of_8_gpus", lambda: mh_bench(ctx, G, CH, 1024, 32, 400, 20, TRUE_TERMS, IG3, 3, -10, 10))
+    guarded("c3_plane_mean_gibbs_64chains_n1024", c3_mean_step)
+    guarded("c5_mcmc_64chains_n8192_se_se_white", lambda: mh_bench(ctx, G, CH, 8192, 64, 32, 2, C5_TERMS, IG5, 5, -15, 15))
     guarded("c4", c4)
     return out
 
 
-def extras_multi_gpu(ctx, G, dist, local):
+def extras_multi_gpu(ctx, G, CH, dist, local):
     """N > 1: the chain-parallel configs (C3 strong: 256 chains over N GPUs; C5 weak: 64 per GPU)."""
     out = {}
     world = dist.get_world_size()
     for name, fn in (
-            ("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, 1024, 256, 100, 5, TRUE_TERMS, IG3, 3, -10, 10, dist, local)),
-            ("c5_mcmc_64chains_per_gpu_n8192_se_se_white", lambda: mh_bench(ctx, G, 8192, 64 * world, 8, 1, C5_TERMS, IG5, 5, -15, 15, dist, local))):
+            ("c3_mcmc_256chains_n1024", lambda: mh_bench(ctx, G, CH, 1024, 256, 400, 20, TRUE_TERMS, IG3, 3, -10, 10, dist, local)),
+            ("c5_mcmc_64chains_per_gpu_n8192_se_se_white", lambda: mh_bench(ctx, G, CH, 8192, 64 * world, 32, 2, C5_TERMS, IG5, 5, -15, 15, dist, local))):
         try:
             out[name] = fn()
         except Exception as e:

@@ -104,6 +104,7 @@ int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
   gg.tgroup = ticket_group(ctx, g);
   const int nl = launch_chol(ctx->stream, gg, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
                              ctx->sched_mode, ctx->num_sms, solve_only, trace);
+  if (nl == -2) return GPB_E_UNSUPPORTED;   // more than 2^31 tiles in one launch
   if (nl < 0) {
     ctx->cuda_err = "cuTensorMapEncodeTiled failed (TMA descriptor of the workspace)";
     return GPB_E_CUDA;

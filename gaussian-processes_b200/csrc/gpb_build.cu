@@ -269,10 +269,16 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
 void launch_build(cudaStream_t st, const Geom& g, const double* x, const double* y,
                   const double* xstar, const Hyper* hyper, double nugget, double* mats, int mode,
                   int full, const double* rows) {
+  static const int num_sms = [] {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    return v > 0 ? v : 148;
+  }();
   const int tiles = full ? g.rt * g.nt : g.nt * (g.nt + 1) / 2 + (g.rt - g.nt) * g.nt;
   // several tiles per CTA once there are enough CTAs to fill the machine a few times over
   int tpc = 1;
-  while (tpc < 8 && (long long)((tiles + 2 * tpc - 1) / (2 * tpc)) * g.batch >= 148 * 4 * 4) tpc *= 2;
+  while (tpc < 8 && (long long)((tiles + 2 * tpc - 1) / (2 * tpc)) * g.batch >= num_sms * 4 * 4) tpc *= 2;
   dim3 grid((tiles + tpc - 1) / tpc, g.batch);
   k_build<<<grid, 256, 0, st>>>(g, x, y, xstar, hyper, nugget, mats, mode, full, rows, tiles, tpc);
 }

@@ -1346,8 +1346,9 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   // per host thread (one gpb_ctx per thread): the attribute is set once per device, and the two TMA
   // descriptors are re-encoded only when the workspace or the geometry changed -- both are pure host
   // latency on every small call otherwise
-  struct Cache { int dev = -1; const double* mats = nullptr; const double* linvt = nullptr; int ld = 0, npad = 0, batch = 0;
+  struct Entry { const double* mats = nullptr; const double* linvt = nullptr; int ld = 0, npad = 0, batch = 0;
                  size_t stride = 0; CUtensorMap tmap, tmapL; };
+  struct Cache { int dev = -1; int next = 0; Entry e[4]; };   // the Mcmc.sample loop alternates two geometries
   thread_local Cache cc;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1355,20 +1356,28 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     cudaFuncSetAttribute(k_chol_tasks<false, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cudaFuncSetAttribute(k_chol_tasks<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cudaFuncSetAttribute(k_chol_tasks<true, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
-    cc.dev = dev; cc.mats = nullptr;
+    cc.dev = dev;
+    for (Entry& e : cc.e) e.mats = nullptr;
   }
   Geom g = g_in;
   if (mode != 0 || g.tgroup < 1 || g.tgroup > g.batch) g.tgroup = g.batch;  // debug mode: one group
-  if (cc.mats != mats || cc.linvt != linvt || cc.ld != g.ld || cc.npad != g.npad || cc.batch != g.batch ||
-      cc.stride != g.mat_stride) {
-    cc.mats = nullptr;
-    if (!make_tmap(&cc.tmap, g, mats)) return -1;
-    if (!make_tmap_linvt(&cc.tmapL, g, linvt)) return -1;
-    cc.mats = mats; cc.linvt = linvt; cc.ld = g.ld; cc.npad = g.npad; cc.batch = g.batch; cc.stride = g.mat_stride;
+  Entry* hit = nullptr;
+  for (Entry& e : cc.e)
+    if (e.mats == mats && e.linvt == linvt && e.ld == g.ld && e.npad == g.npad && e.batch == g.batch && e.stride == g.mat_stride) hit = &e;
+  if (!hit) {
+    hit = &cc.e[cc.next];
+    cc.next = (cc.next + 1) % 4;
+    hit->mats = nullptr;
+    if (!make_tmap(&hit->tmap, g, mats)) return -1;
+    if (!make_tmap_linvt(&hit->tmapL, g, linvt)) return -1;
+    hit->mats = mats; hit->linvt = linvt; hit->ld = g.ld; hit->npad = g.npad; hit->batch = g.batch; hit->stride = g.mat_stride;
   }
-  const CUtensorMap& tmap = cc.tmap;
-  const CUtensorMap& tmapL = cc.tmapL;
+  const CUtensorMap& tmap = hit->tmap;
+  const CUtensorMap& tmapL = hit->tmapL;
   const long long total = (long long)g.batch * ((long long)g.nt * g.rt - (long long)g.nt * (g.nt - 1) / 2);
+  // tickets are 32-bit inside the kernel (one atomic counter, decode_task): refuse what would not fit
+  // instead of truncating (64 chains x n=8192 are 5.4e5 tickets, n=32768 alone 1.3e5)
+  if (total > 0x7fff0000LL) return -2;
   int launches = 0;
   {
     const long long total = (long long)g.batch * (g.rt + g.nt);

@@ -315,6 +315,8 @@ extern "C" int gpb_mll_gradient(gpb_ctx* ctx, const gpb_dataset* ds, int batch, 
     std::memset(&sp, 0, sizeof(sp));
     for (int t = 0; t < nterms; ++t) {
       const gpb_term& th = terms[(size_t)b * nterms + t];
+      // grad is [batch][P] with P taken from element 0: every element must share its term structure
+      if (th.kind != terms[t].kind) return GPB_E_INVALID;
       kt[t] = th;
       if (th.kind == GPB_KIND_SE) {
         const double s = std::exp(th.p1);

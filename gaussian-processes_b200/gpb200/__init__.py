@@ -9,6 +9,8 @@ on the CPU.  The Scala binding a maintainer would add is in INTEGRATION.md / sca
 from .api import (  # noqa: F401
     One, Two, Location, SquaredExp, White, Matern, KernelParameters, Zero, Plane, MeanParameters,
     MeanFunction, KernelFunction, GaussianProcess, Predict, Mcmc, Gaussian, NotConvergedException,
-    default_context, set_default_device, Hmc, GradDist, Ehmc, DualAverage, DualAverageState,
+    default_context, set_default_device,
 )
+# out-of-scope samplers around the in-scope gradient (frozen; see extras_hmc.py)
+from .extras_hmc import Hmc, GradDist, Ehmc, DualAverage, DualAverageState  # noqa: F401,E402
 from ._lib import GpbError, FORMULA_AS_PARSED, FORMULA_GPML, GRAD_AS_EXECUTED, GRAD_ANALYTIC  # noqa: F401

@@ -10,6 +10,9 @@
 //   MeanParameters.samplePlane     MeanParameters.scala:74-103    -> Gpb200.samplePlane
 //   GaussianProcess.draw           GaussianProcess.scala:67-83    -> Gpb200.draw
 //   GaussianProcess.mllGradient    GaussianProcess.scala:166-187  -> Gpb200.mllGradient
+//   Mcmc.sample (many chains)      Mcmc.scala:63-76               -> Gpb200.mhRunEx (device resident)
+//   Streaming.writeParallelChain   SimulatedGp.scala:163-165      -> Gpb200.commUniqueId / commInitRank /
+//                                                                    commShard + mhRunEx(gather = 1)
 package com.github.jonnylaw.gp
 
 import java.lang.foreign._
@@ -213,5 +216,88 @@ object Gpb200 {
         grad.toArray(JAVA_DOUBLE)
       } finally a.close()
     }
+  }
+
+  // ---- Mcmc.sample for many chains, device resident (gpb_mh_run_ex), and the multi-GPU gather ------------
+  // struct gpb_mh_config (include/gpb200.h): ints and doubles in declaration order, natural alignment
+  private val MHCFG = MemoryLayout.structLayout(
+    JAVA_INT.withName("struct_size"), JAVA_INT.withName("formula"), JAVA_INT.withName("on_notpd"), JAVA_INT.withName("rng"),
+    JAVA_DOUBLE.withName("delta"), JAVA_DOUBLE.withName("nugget"), JAVA_LONG.withName("seed"),
+    JAVA_INT.withName("chain0"), JAVA_INT.withName("mean_step"),
+    JAVA_DOUBLE.withName("mean_prior_mean"), JAVA_DOUBLE.withName("mean_prior_var"), JAVA_DOUBLE.withName("mean_nugget"),
+    JAVA_INT.withName("flush_every"), JAVA_INT.withName("gather"), JAVA_INT.withName("total_chains"), JAVA_INT.withName("small_n"))
+  // struct gpb_mh_result { int info, stopped_chains, path, flushes; float device_ms; }
+  private val MHRES = MemoryLayout.structLayout(JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_FLOAT)
+  private val mhRunExH = fn("gpb_mh_run_ex", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT,
+    ADDRESS, JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS))
+  private val commIdH = fn("gpb_comm_unique_id", FunctionDescriptor.of(JAVA_INT, ADDRESS))
+  private val commInitH = fn("gpb_comm_init_rank", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS))
+  private val commShardH = fn("gpb_comm_shard", FunctionDescriptor.of(JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS))
+
+  case class MhConfig(delta: Double = 0.05, formula: Int = 0, onNotPd: Int = 0, seed: Long = 0L, chain0: Int = 0,
+                      meanStep: Boolean = false, priorMean: Gaussian = Gaussian(0, 1), flushEvery: Int = 0,
+                      gather: Boolean = false, totalChains: Int = 0)
+  case class Chains(states: Array[Double] /* [iters][C][W] */, ll: Array[Double], accept: Array[Int], stop: Array[Int])
+
+  /** The 128-byte communicator id: create it once, hand it to every rank's thread. */
+  def commUniqueId(): Array[Byte] = {
+    val a = Arena.ofConfined()
+    try { val id = a.allocate(128); check(commIdH.invoke(id).asInstanceOf[Int]); id.toArray(JAVA_BYTE) } finally a.close()
+  }
+  /** One rank = one thread = one ctx = one device (the threading model of SimulatedGp.scala:163-165). */
+  def commInitRank(nranks: Int, rank: Int, id: Array[Byte]): Unit = {
+    val a = Arena.ofConfined()
+    try check(commInitH.invoke(ctx.get, nranks, rank, a.allocateFrom(JAVA_BYTE, id: _*)).asInstanceOf[Int]) finally a.close()
+  }
+  def commShard(total: Int, nranks: Int, rank: Int): (Int, Int) = {
+    val a = Arena.ofConfined()
+    try {
+      val f = a.allocate(JAVA_INT); val c = a.allocate(JAVA_INT)
+      check(commShardH.invoke(total, nranks, rank, f, c).asInstanceOf[Int]); (f.get(JAVA_INT, 0), c.get(JAVA_INT, 0))
+    } finally a.close()
+  }
+
+  /** Mcmc.sample(ys, priorKern, priorMean, propKern, dist, initP) for `inits.size` chains on this thread's
+    * device, with the shipped example's proposal (log-normal random walk, step delta) and inverse-gamma priors
+    * `ig` = (shape, scale) per kernel parameter; device Philox streams.  With cfg.gather every rank's call returns
+    * the chains of ALL ranks (NCCL all-gather of every ring segment inside the library). */
+  def mhRunEx(observed: Vector[Data], dist: (Location[Double], Location[Double]) => Double, inits: Vector[Parameters],
+              ig: Vector[(Double, Double)], iters: Int, cfg: MhConfig): Chains = {
+    requireEuclidean(dist)
+    val a = Arena.ofConfined()
+    try {
+      val (x, dim) = soa(observed.map(_.x), a)
+      val y = a.allocateFrom(JAVA_DOUBLE, observed.map(_.y): _*)
+      val dsOut = a.allocate(ADDRESS)
+      check(dsCreate.invoke(ctx.get, observed.size, dim, x, y, dsOut).asInstanceOf[Int])
+      val ds = dsOut.get(ADDRESS, 0)
+      val nterms = inits.head.kernelParameters.size
+      val P = inits.head.kernelParameters.map(_.toList.size).sum
+      val nbeta = inits.head.meanParameters.toList.size
+      val d = if (cfg.meanStep) nbeta else 0
+      val c = MHCFG.byteSize(); val m = a.allocate(MHCFG)
+      m.set(JAVA_INT, 0, c.toInt); m.set(JAVA_INT, 4, cfg.formula); m.set(JAVA_INT, 8, cfg.onNotPd); m.set(JAVA_INT, 12, 1 /* GPB_RNG_PHILOX */)
+      m.set(JAVA_DOUBLE, 16, cfg.delta); m.set(JAVA_DOUBLE, 24, 1e-3); m.set(JAVA_LONG, 32, cfg.seed)
+      m.set(JAVA_INT, 40, cfg.chain0); m.set(JAVA_INT, 44, if (cfg.meanStep) 1 else 0)
+      m.set(JAVA_DOUBLE, 48, cfg.priorMean.mean); m.set(JAVA_DOUBLE, 56, cfg.priorMean.variance); m.set(JAVA_DOUBLE, 64, 1e-6)
+      m.set(JAVA_INT, 72, cfg.flushEvery); m.set(JAVA_INT, 76, if (cfg.gather) 1 else 0); m.set(JAVA_INT, 80, cfg.totalChains); m.set(JAVA_INT, 84, 0)
+      val termsAll = a.allocate(TERM, inits.size.toLong * nterms)
+      inits.zipWithIndex.foreach { case (p, i) => MemorySegment.copy(terms(p.kernelParameters, a), 0, termsAll, i.toLong * nterms * TERM.byteSize(), nterms * TERM.byteSize()) }
+      val beta0 = if (nbeta == 0) MemorySegment.NULL else a.allocateFrom(JAVA_DOUBLE, inits.flatMap(_.meanParameters.toList): _*)
+      val design = if (!cfg.meanStep) MemorySegment.NULL
+                   else a.allocateFrom(JAVA_DOUBLE, MeanParameters.makeDesignMatrix(observed.map(_.x).distinct).toArray: _*)  // column-major [d][n]
+      val C = if (cfg.gather) cfg.totalChains else inits.size
+      val W = P + d
+      val st = a.allocate(JAVA_DOUBLE, iters.toLong * C * W); val ll = a.allocate(JAVA_DOUBLE, iters.toLong * C)
+      val acc = a.allocate(JAVA_INT, iters.toLong * C); val stop = a.allocate(JAVA_INT, C.toLong); val res = a.allocate(MHRES)
+      val rc = mhRunExH.invoke(ctx.get, ds, m, inits.size, iters, termsAll, nterms, beta0, nbeta,
+        a.allocateFrom(JAVA_DOUBLE, ig.flatMap(t => Seq(t._1, t._2)): _*), MemorySegment.NULL, MemorySegment.NULL, design,
+        st, ll, acc, stop, res).asInstanceOf[Int]
+      dsDestroy.invoke(ds)
+      if (rc == -7) // GPB_E_NOTPD: `cholesky` threw on some chain's thread in the reference
+        throw new breeze.linalg.NotConvergedException(breeze.linalg.NotConvergedException.Divergence)
+      check(rc)
+      Chains(st.toArray(JAVA_DOUBLE), ll.toArray(JAVA_DOUBLE), acc.toArray(JAVA_INT), stop.toArray(JAVA_INT))
+    } finally a.close()
   }
 }

@@ -69,6 +69,30 @@ def test_philox_streams_are_counter_based():
                                 uu.ctypes.data_as(C.POINTER(C.c_double))) == 0
 
 
+def test_mh_config_layout_is_the_published_one():
+    """gpb_mh_config / gpb_mh_result as a Panama / JNI binding must lay them out (INTEGRATION.md,
+    scala/Gpb200.scala): natural alignment, 88 and 20 bytes."""
+    from gpb200 import _lib as G
+    off = {f[0]: getattr(G.MhConfig, f[0]).offset for f in G.MhConfig._fields_}
+    assert off == {"struct_size": 0, "formula": 4, "on_notpd": 8, "rng": 12, "delta": 16, "nugget": 24, "seed": 32,
+                   "chain0": 40, "mean_step": 44, "mean_prior_mean": 48, "mean_prior_var": 56, "mean_nugget": 64,
+                   "flush_every": 72, "gather": 76, "total_chains": 80, "small_n": 84}
+    assert C.sizeof(G.MhConfig) == 88 and C.sizeof(G.MhResult) == 20
+
+
+def test_comm_entry_points_without_a_device():
+    """Host-only parts of the multi-GPU ABI: the block partition, and loud refusals (no emulation)."""
+    from gpb200 import _lib as G
+    L = G.load()
+    assert [G.comm_shard(256, 8, r) for r in (0, 7)] == [(0, 32), (224, 32)]
+    assert [G.comm_shard(10, 4, r) for r in range(4)] == [(0, 3), (3, 3), (6, 2), (8, 2)]
+    with pytest.raises(G.GpbError):
+        G.comm_shard(10, 4, 4)
+    assert L.gpb_comm_init_rank(None, 2, 0, None) == -1          # GPB_E_INVALID
+    assert L.gpb_mh_run_ex(None, None, None, 1, 1, None, 1, None, 0, None, None, None, None, None, None, None, None, None) == -1
+    assert b"communicator" in L.gpb_strerror(-8)
+
+
 def test_strerror_and_version():
     from gpb200 import _lib as G
     L = G.load()

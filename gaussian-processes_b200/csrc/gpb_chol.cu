@@ -561,7 +561,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
     mbar_fence_init();
     sm.pause_mine = sm.pause_other = nullptr;
-    if (chain_pause) {
+    if (MINB == 2 && chain_pause) {   // the one-CTA-per-SM instantiation has no neighbour to pause
       // which of the (up to two) CTAs of this SM am I?  Arrival order on a per-SM counter.
       const unsigned sid = smid() % SCHED_MAXSM;
       const int slot = atomicAdd(&sched->smslot[sid], 1) & 1;
@@ -596,10 +596,10 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     int t_next = (lane == 0) ? fetch() : 0;
     // chain_pause: do not feed this CTA's contraction while the CTA that shares the SM is inside a
     // critical section (advisory: bounded, and publications keep being served)
-    int* const pause_mine = sm.pause_mine;
-    int* const pause_other = sm.pause_other;
+    int* const pause_mine = (MINB == 2) ? sm.pause_mine : nullptr;
+    int* const pause_other = (MINB == 2) ? sm.pause_other : nullptr;
     auto hold_while_paused = [&]() {
-      if (pause_other == nullptr || *(volatile int*)pause_other <= 0) return;
+      if (MINB != 2 || pause_other == nullptr || *(volatile int*)pause_other <= 0) return;
       const long long t0 = clock64();
       while (*(volatile int*)pause_other > 0) {
         service_release(sm, rs);
@@ -707,7 +707,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
             if (d.j > 0) wait_counter_serving(part_b + d.i, 1, &sched->error, sm, rs);
             fence_proxy_async();
             // everything the critical section needs exists: the SM is this CTA's until the block is factored
-            if (pause_mine != nullptr) atomicAdd(pause_mine, 1);
+            if (MINB == 2 && pause_mine != nullptr) atomicAdd(pause_mine, 1);
 #pragma unroll 1
             for (int s = 0; s < AT_STAGES; ++s) {
               if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
@@ -721,7 +721,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
           }
         } else if (!solve_only) {
           // diagonal task: LT_STAGES stages as scratch for the stacked inverse rows
-          if (pause_mine != nullptr) atomicAdd(pause_mine, 1);
+          if (MINB == 2 && pause_mine != nullptr) atomicAdd(pause_mine, 1);
           load_identity();
         }
         // the next ticket is drawn only now, behind every load of this task: see `fetch` above
@@ -1041,7 +1041,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       } else {
         post_release(done_b + dj, dj + 1);
       }
-      if (tid == 0 && sm.pause_mine != nullptr) atomicSub(sm.pause_mine, 1);   // end of the critical section
+      if (MINB == 2 && tid == 0 && sm.pause_mine != nullptr) atomicSub(sm.pause_mine, 1);   // end of the critical section
       fence_proxy_async();             // generic writes to the scratch stages before TMA refills them
       __syncwarp();
       if (lane == 0)
@@ -1395,7 +1395,10 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     if (env_ctas < 0) { const char* e = getenv("GPB_CTAS_PER_SM_RT"); env_ctas = e ? atoi(e) : 0; }
     int ctas = (total >= 24LL * num_sms) ? CTAS_PER_SM : 1;
     if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
-    const long long slots = (long long)num_sms * ctas;
+    // GPB_GRID_CAP=k (tuning): at most k CTAs per SM in the grid while keeping the instantiation `ctas` selects
+    static int env_cap = -1;
+    if (env_cap < 0) { const char* e = getenv("GPB_GRID_CAP"); env_cap = e ? atoi(e) : 0; }
+    const long long slots = (long long)num_sms * ((env_cap > 0 && env_cap < ctas) ? env_cap : ctas);
     int grid = (int)(total < slots ? total : slots);
     // Two CTAs per SM, but still few enough tasks per SM that the chain diag(j) -> (j+1, j) -> diag(j+1)
     // bounds part of the launch: the CTA inside a block column's critical section gets the SM to itself

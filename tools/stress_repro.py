@@ -8,7 +8,7 @@ from gpb200 import _lib as G
 ctx = G.Context(0)
 rng = np.random.default_rng(11)
 bad_total = 0
-for n, B, reps in [(4096, 8, 12), (4096, 1, 12), (1024, 64, 20), (8192, 2, 4), (300, 16, 20)]:
+for n, B, reps in [(4096, 8, 12), (4096, 1, 12), (4096, 2, 12), (4096, 3, 8), (2048, 8, 12), (1024, 32, 20), (1024, 64, 20), (8192, 2, 4), (300, 16, 20)]:
     x = rng.uniform(-10, 10, size=(n, 2)); y = rng.standard_normal(n)
     ds = ctx.dataset(x, y)
     props = [[(0, 3.0 * math.exp(0.05 * rng.standard_normal()), 5.5), (1, 0.5, 0.0)] for _ in range(B)]
@@ -26,4 +26,4 @@ for n, B, reps in [(4096, 8, 12), (4096, 1, 12), (1024, 64, 20), (8192, 2, 4), (
     print(f"n={n} B={B}: {bad}/{reps} runs differ from the per-phase scheduler; infos {sorted(set(r[3] for r in ref))}")
     bad_total += bad
     ds.close()
-print("TOTAL_BAD", bad_total)
+print("pause", os.environ.get("GPB_CHAIN_PAUSE", "auto"), "TOTAL_BAD", bad_total)

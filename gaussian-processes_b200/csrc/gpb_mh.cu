@@ -124,7 +124,7 @@ __device__ __forceinline__ double mh_prior(const MhDev& md, const double* __rest
   return pr;
 }
 __device__ __forceinline__ double mh_ll_value(const MhDev& md, double Q, double U1, double S) {
-  const double C = md.n * 0.5 * log(2 * M_PI);
+  const double C = md.n * 0.9189385332046727;   // n/2 log(2 pi)
   return md.formula == GPB_FORMULA_GPML ? (-0.5 * Q - S - C) : (-0.5 * Q + 0.5 * (S + C) * U1);
 }
 // Breeze metropolis with JVM semantics: scala.math.min propagates NaN and `u < NaN` is false.
@@ -255,10 +255,11 @@ __global__ void k_mh_accept(MhDev md, MhState s, int it, const gpb_ll* __restric
 struct TinySmem {
   double A[TINY_N * TINY_LD];   // column-major [c][r], rows 0..n-1 the matrix, row n the rhs
   double x[2][TINY_N], y[TINY_N];
-  double piv[TINY_N + 1];
+  double piv;
   double red[3][TINY_THREADS / 32];
-  double cur[MAXP], prop[MAXP], beta[3];
-  double cur_ll, new_ll;
+  double cur[MAXP], prop[MAXP], pterm[MAXP], beta[3];
+  double cur_ll, uni;
+  double ninv2[MAXT];           // -1 / sigma^2 per squared-exponential term
   Hyper h;
   int info;
 };
@@ -267,42 +268,75 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
-// log-likelihood reductions of the system for sm.h (info in sm.info); every thread returns them.
+// Log-likelihood reductions of the system for sm.h (info in sm.info); every thread returns them.
+// blockDim.x = the n + 1 stacked rows rounded up to whole warps: at n = 20 every barrier is one warp.
 __device__ void tiny_eval(const MhDev& md, TinySmem& sm, double& Q, double& U1, double& S) {
-  const int tid = threadIdx.x, n = md.n;
-  // covariance, lower triangle + rhs row (KernelFunction.buildCov + nugget; residual y - m(x))
-  for (int e = tid; e < n * (n + 1); e += TINY_THREADS) {
-    const int c = e / (n + 1), r = e % (n + 1);
-    if (r < c) continue;
-    double v;
-    if (r < n) {
-      v = cov_of_dist(sm.h, euclid(md.dim, sm.x[0][r], sm.x[1][r], sm.x[0][c], sm.x[1][c]));
-      if (r == c) v = __dadd_rn(v, md.nugget);
-    } else {
-      double mu = 0.0;
-      if (sm.h.nbeta > 0) {
-        mu = __dadd_rn(sm.h.beta[0], __dmul_rn(sm.x[0][c], sm.h.beta[1]));
-        if (md.dim == 2) mu = __dadd_rn(mu, __dmul_rn(sm.x[1][c], sm.h.beta[2]));
-      }
-      v = sm.y[c] - mu;
+  const int tid = threadIdx.x, n = md.n, nthr = blockDim.x;
+  // covariance, lower triangle (KernelFunction.buildCov + nugget), entries dealt out linearly; the
+  // hot-path form of k_build (h exp(d^2 (-1/s^2)): no sqrt / division per entry, <= 2 ulp(h) from the
+  // reference's operation order, tests/test_gpu_parity.py::test_hot_path_build_entrywise)
+  const int tri = n * (n + 1) / 2;
+  for (int e = tid; e < tri; e += nthr) {
+    int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+    while (r * (r + 1) / 2 > e) --r;
+    while ((r + 1) * (r + 2) / 2 <= e) ++r;
+    const int c = e - r * (r + 1) / 2;
+    const double dx = sm.x[0][r] - sm.x[0][c];
+    double d2 = __dmul_rn(dx, dx);
+    if (md.dim == 2) { const double dy = sm.x[1][r] - sm.x[1][c]; d2 = __dadd_rn(d2, __dmul_rn(dy, dy)); }
+    double v = 0.0;
+    for (int t = 0; t < sm.h.nterms; ++t) {
+      const double term = (sm.h.kind[t] == GPB_KIND_SE) ? sm.h.p0[t] * exp(d2 * sm.ninv2[t]) : ((d2 == 0.0) ? sm.h.p0[t] : 0.0);
+      v = __dadd_rn(v, term);
     }
+    if (r == c) v = __dadd_rn(v, md.nugget);
     sm.A[c * TINY_LD + r] = v;
+  }
+  for (int c = tid; c < n; c += nthr) {   // rhs row: residual y - m(x)
+    double mu = 0.0;
+    if (sm.h.nbeta > 0) {
+      mu = __dadd_rn(sm.h.beta[0], __dmul_rn(sm.x[0][c], sm.h.beta[1]));
+      if (md.dim == 2) mu = __dadd_rn(mu, __dmul_rn(sm.x[1][c], sm.h.beta[2]));
+    }
+    sm.A[c * TINY_LD + n] = sm.y[c] - mu;
   }
   if (tid == 0) sm.info = 0;
   __syncthreads();
-  // column j: s_i = a_ij - sum_{k<j} l_ik l_jk for the rows i >= j (row n: the rhs), then scale
+  // column j: s_i = a_ij - sum_{k<j} l_ik l_jk for the rows i >= j (row n: the rhs), then scale by
+  // 1/sqrt(pivot) (hardware approximation + two Newton steps, as in the diagonal blocks of k_chol_tasks:
+  // the IEEE sqrt and division subroutines are most of a column's dependency chain at this size)
   for (int j = 0; j < n; ++j) {
     double s = 0.0;
     if (tid >= j && tid <= n) {
-      s = sm.A[j * TINY_LD + tid];
-      for (int k = 0; k < j; ++k) s = fma(-sm.A[k * TINY_LD + tid], sm.A[k * TINY_LD + j], s);
-      if (tid == j) sm.piv[0] = s;
+      // four partial sums, eight loads in flight: the loop is bound by shared-memory latency otherwise
+      double s0 = sm.A[j * TINY_LD + tid], s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      const double* ai = &sm.A[tid];
+      const double* aj = &sm.A[j];
+      int k = 0;
+#pragma unroll 2
+      for (; k + 3 < j; k += 4) {
+        const double x0 = ai[k * TINY_LD], x1 = ai[(k + 1) * TINY_LD], x2 = ai[(k + 2) * TINY_LD], x3 = ai[(k + 3) * TINY_LD];
+        const double y0 = aj[k * TINY_LD], y1 = aj[(k + 1) * TINY_LD], y2 = aj[(k + 2) * TINY_LD], y3 = aj[(k + 3) * TINY_LD];
+        s0 = fma(-x0, y0, s0); s1 = fma(-x1, y1, s1); s2 = fma(-x2, y2, s2); s3 = fma(-x3, y3, s3);
+      }
+      for (; k < j; ++k) s0 = fma(-ai[k * TINY_LD], aj[k * TINY_LD], s0);
+      s = (s0 + s1) + (s2 + s3);
+      if (tid == j) sm.piv = s;
     }
     __syncthreads();
-    const double a = sm.piv[0];
+    const double a = sm.piv;
     if (!(a > 0.0)) { if (tid == 0) sm.info = j + 1; break; }   // uniform: every thread reads the same pivot
-    const double dj = sqrt(a);
-    if (tid >= j && tid <= n) sm.A[j * TINY_LD + tid] = (tid == j) ? dj : s / dj;
+    double rs;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(rs) : "d"(a));
+    double e1 = fma(-(a * rs), rs, 1.0);
+    rs = fma(0.5 * rs, e1, rs);
+    e1 = fma(-(a * rs), rs, 1.0);
+    rs = fma(0.5 * rs, e1, rs);
+    if (tid >= j && tid <= n) {
+      double l = s * rs;
+      if (tid == j) { const double sv = a * rs; l = fma(0.5 * rs, fma(-sv, sv, a), sv); }   // sqrt(a) to ~0.5 ulp
+      sm.A[j * TINY_LD + tid] = l;
+    }
     __syncthreads();
   }
   __syncthreads();
@@ -315,15 +349,15 @@ __device__ void tiny_eval(const MhDev& md, TinySmem& sm, double& Q, double& U1, 
   if ((tid & 31) == 0) { sm.red[0][tid >> 5] = q; sm.red[1][tid >> 5] = u1; sm.red[2][tid >> 5] = sl; }
   __syncthreads();
   Q = U1 = S = 0.0;
-  for (int w = 0; w < TINY_THREADS / 32; ++w) { Q += sm.red[0][w]; U1 += sm.red[1][w]; S += sm.red[2][w]; }
-  __syncthreads();
+  for (int w = 0; w < (nthr >> 5); ++w) { Q += sm.red[0][w]; U1 += sm.red[1][w]; S += sm.red[2][w]; }
 }
+
 __global__ void __launch_bounds__(TINY_THREADS)
 k_mh_tiny(MhDev md, MhState s, const double* __restrict__ x, const double* __restrict__ y, int it0, int count,
           int first, double* __restrict__ ring) {
   __shared__ TinySmem sm;
   const int c = blockIdx.x, tid = threadIdx.x, n = md.n;
-  for (int i = tid; i < n; i += TINY_THREADS) {
+  for (int i = tid; i < n; i += blockDim.x) {
     sm.x[0][i] = x[i];
     sm.x[1][i] = (md.dim == 2) ? x[n + i] : 0.0;
     sm.y[i] = y[i];
@@ -339,10 +373,19 @@ k_mh_tiny(MhDev md, MhState s, const double* __restrict__ x, const double* __res
       if (tid == 0 && row) write_dead_row(md, row, dinfo);
       continue;
     }
+    // one lane per parameter: its normal, its proposal, its prior term; one more lane draws the uniform
+    if (tid < md.P) {
+      const double v = (it >= 0) ? sm.cur[tid] * exp(md.delta * mh_normal(md, s.z, it, c, tid)) : sm.cur[tid];
+      sm.prop[tid] = v;
+      sm.pterm[tid] = ig_logpdf(md, tid, v);
+    } else if (tid == md.P && it >= 0) {
+      sm.uni = mh_uniform(md, s.uu, it, c);
+    }
+    __syncthreads();
     if (tid == 0) {
-      for (int p = 0; p < md.P; ++p)
-        sm.prop[p] = (it >= 0) ? sm.cur[p] * exp(md.delta * mh_normal(md, s.z, it, c, p)) : sm.cur[p];
       fill_hyper_dev(md, sm.prop, sm.beta, md.nbeta, sm.h);
+      for (int t = 0; t < md.nterms; ++t)
+        sm.ninv2[t] = (md.kind[t] == GPB_KIND_SE) ? -1.0 / (sm.h.p1[t] * sm.h.p1[t]) : 0.0;
     }
     __syncthreads();
     double Q, U1, S;
@@ -353,15 +396,21 @@ k_mh_tiny(MhDev md, MhState s, const double* __restrict__ x, const double* __res
       if (!md.on_notpd) {
         dead = (it < 0 ? 0 : it) + 1; dinfo = bad;
         if (tid == 0 && row) write_dead_row(md, row, bad);
+        __syncthreads();
         continue;
       }
     }
     if (tid == 0) {
-      const double new_ll = (bad == 0) ? mh_prior(md, sm.prop) + mh_ll_value(md, Q, U1, S) : NAN;
+      double pr = 0.0;   // priorKernel in the reference's order: ps.map(...).sum (SimulatedGp.scala:143-151)
+      for (int t = 0, p = 0; t < md.nterms; ++t) {
+        if (md.kind[t] == GPB_KIND_SE) { pr = pr + (sm.pterm[p] + sm.pterm[p + 1]); p += 2; }
+        else { pr = pr + sm.pterm[p]; p += 1; }
+      }
+      const double new_ll = (bad == 0) ? pr + mh_ll_value(md, Q, U1, S) : NAN;
       if (it < 0) {
         sm.cur_ll = new_ll;
       } else {
-        const bool acc = (bad == 0) && mh_accepts(new_ll, sm.cur_ll, mh_uniform(md, s.uu, it, c));
+        const bool acc = (bad == 0) && mh_accepts(new_ll, sm.cur_ll, sm.uni);
         if (acc) {
           for (int p = 0; p < md.P; ++p) sm.cur[p] = sm.prop[p];
           sm.cur_ll = new_ll;
@@ -374,7 +423,6 @@ k_mh_tiny(MhDev md, MhState s, const double* __restrict__ x, const double* __res
   if (tid < md.P) s.cur[(size_t)c * md.P + tid] = sm.cur[tid];
   if (tid == 0) { s.cur_ll[c] = sm.cur_ll; s.dead[c] = dead; s.dinfo[c] = dinfo; }
 }
-
 // Segment trailer: [first_bad] so that the flushed (and gathered) data carries the status with it.
 __global__ void k_mh_trailer(const int* __restrict__ first_bad, double* __restrict__ trailer) {
   trailer[0] = (double)*first_bad;
@@ -575,7 +623,9 @@ int gpb_mh_run_ex(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_mh_config* cfg_
       CK(cudaStreamWaitEvent(st, ctx->ev_flushed[b], 0));
     }
     if (tiny) {
-      k_mh_tiny<<<chains, TINY_THREADS, 0, st>>>(md, s, ds->x, ds->y, it0, cnt, sg == 0 ? 1 : 0, ring[b]);
+      // the n + 1 stacked rows (and the P + 1 sampling lanes) rounded up to whole warps
+      const int tthreads = 32 * ((std::max(ds->n + 1, P + 1) + 31) / 32);
+      k_mh_tiny<<<chains, tthreads, 0, st>>>(md, s, ds->x, ds->y, it0, cnt, sg == 0 ? 1 : 0, ring[b]);
       ctx->launches += 1;
     } else {
       for (int it = (sg == 0 ? -1 : it0); it < it0 + cnt; it = (it < 0 ? it0 : it + 1)) {

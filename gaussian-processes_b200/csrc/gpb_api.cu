@@ -91,7 +91,7 @@ static int ticket_group(const gpb_ctx* ctx, const Geom& g) {
   return g.batch;
 }
 
-int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
+int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only, int skip_reset) {
   unsigned long long* trace = nullptr;
   if (ctx->trace_on) {
     ctx->trace_tasks = chol_task_count(g);
@@ -103,7 +103,7 @@ int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only) {
   Geom gg = g;
   gg.tgroup = ticket_group(ctx, g);
   const int nl = launch_chol(ctx->stream, gg, ctx->mats, ctx->linvt, ctx->done, ctx->info, ctx->sched,
-                             ctx->sched_mode, ctx->num_sms, solve_only, trace);
+                             ctx->sched_mode, ctx->num_sms, solve_only, trace, -1, skip_reset);
   if (nl == -2) return GPB_E_UNSUPPORTED;   // more than 2^31 tiles in one launch
   if (nl < 0) {
     ctx->cuda_err = "cuTensorMapEncodeTiled failed (TMA descriptor of the workspace)";

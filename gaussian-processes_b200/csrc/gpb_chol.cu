@@ -1342,7 +1342,7 @@ long long chol_schedule_task(const Geom& g_in, long long ticket, int* out4) {
 
 int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, int* done, int* info,
                 SchedState* sched, int mode, int num_sms, int solve_only, unsigned long long* trace,
-                int chain_pause) {
+                int chain_pause, int skip_reset) {
   // per host thread (one gpb_ctx per thread): the attribute is set once per device, and the two TMA
   // descriptors are re-encoded only when the workspace or the geometry changed -- both are pure host
   // latency on every small call otherwise
@@ -1379,7 +1379,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   // instead of truncating (64 chains x n=8192 are 5.4e5 tickets, n=32768 alone 1.3e5)
   if (total > 0x7fff0000LL) return -2;
   int launches = 0;
-  {
+  if (!skip_reset || mode != 0) {
     const long long total = (long long)g.batch * (g.rt + g.nt);
     const int blocks = (int)((total + 255) / 256 < 296 ? (total + 255) / 256 : 296);
     k_chol_reset<<<blocks, 256, 0, st>>>(g, done, info, sched, linvt);

@@ -92,7 +92,7 @@ int run_system(gpb_ctx* ctx, const Geom& g, const double* d_x, const double* d_y
                const double* d_xstar, double nugget);
 int finish_timing(gpb_ctx* ctx);
 // Launch the factorisation / panel-solve kernel(s) on ctx->stream; counts launches; status out.
-int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only);
+int do_chol(gpb_ctx* ctx, const Geom& g, int solve_only, int skip_reset = 0);
 // gpb_comm.cu: all-gather `count` doubles per rank, device to device, on `st` (recv: [nranks][count]).
 int comm_allgather(gpb_ctx* ctx, const double* d_send, double* d_recv, size_t count, cudaStream_t st);
 void comm_release(gpb_ctx* ctx);

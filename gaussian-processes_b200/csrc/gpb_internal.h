@@ -33,7 +33,9 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 // Returns the number of kernel launches issued.
 int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int* done,
                 int* info, SchedState* sched, int mode, int num_sms, int solve_only = 0,
-                unsigned long long* trace = nullptr, int chain_pause = -1);
+                unsigned long long* trace = nullptr, int chain_pause = -1, int skip_reset = 0);
+// skip_reset: the caller has already zeroed the scheduler state of this launch (the MH loop's step kernel
+// does it for the next iteration: one launch less per iteration)
 constexpr int CHOL_TRACE_SLOTS = 14;
 long long chol_task_count(const Geom& g);
 // ticket -> {proposal, tile row, tile column, kind}; returns the number of tickets

@@ -247,6 +247,88 @@ __global__ void k_mh_accept(MhDev md, MhState s, int it, const gpb_ll* __restric
   write_row(md, row, cur, s.beta + (size_t)c * 3, old_ll, acc ? 1.0 : 0.0);
 }
 
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// Fixed mean: everything between two factorisations in ONE kernel, one CTA per chain -- the likelihood
+// reductions of the finished system (k_ll_epilogue's sums in the same order), the accept step, the NEXT
+// proposal with its hyper-parameters, and the reset of k_chol_tasks' scheduler state for the next launch.
+// An iteration is then three launches: k_build, k_chol_tasks, k_mh_step.
+__global__ void __launch_bounds__(256)
+k_mh_step(MhDev md, MhState s, Geom g, int it, int propose_next, const double* __restrict__ mats,
+          int* __restrict__ info, int* __restrict__ done, SchedState* sched, Hyper* __restrict__ hyper,
+          double* __restrict__ ring_rows) {
+  const int c = blockIdx.x, tid = threadIdx.x;
+  const double* M = mats + (size_t)c * g.mat_stride;
+  double q = 0.0, u1 = 0.0, sl = 0.0;
+  for (int col = tid; col < g.n; col += blockDim.x) {
+    const double u = M[(size_t)col * g.ld + g.rhs_row];
+    const double l = M[(size_t)col * g.ld + col];
+    q = fma(u, u, q); u1 += u; sl += log(l);
+  }
+  __shared__ double red[3][8];
+  __shared__ double sprop[MAXP];
+  __shared__ int alive;
+  q = warp_sum_d(q); u1 = warp_sum_d(u1); sl = warp_sum_d(sl);
+  if ((tid & 31) == 0) { red[0][tid >> 5] = q; red[1][tid >> 5] = u1; red[2][tid >> 5] = sl; }
+  __syncthreads();
+  double* cur = s.cur + (size_t)c * md.P;
+  double* prop = s.prop + (size_t)c * md.P;
+  if (tid == 0) {
+    double Q = 0, U1 = 0, S = 0;
+    for (int i = 0; i < 8; ++i) { Q += red[0][i]; U1 += red[1][i]; S += red[2][i]; }
+    double* row = (it >= 0) ? ring_rows + (size_t)c * md.RW : nullptr;
+    int bad = info[c];
+    if (s.dead[c]) {
+      if (row) write_dead_row(md, row, s.dinfo[c]);
+    } else {
+      if (bad != 0) atomicCAS(s.first_bad, 0, bad);
+      if (bad != 0 && !md.on_notpd) {          // mirror: this chain ends here (the reference throws)
+        s.dead[c] = (it < 0 ? 0 : it) + 1; s.dinfo[c] = bad;
+        if (row) write_dead_row(md, row, bad);
+      } else {
+        const double new_ll = (bad == 0) ? mh_prior(md, prop) + mh_ll_value(md, Q, U1, S) : NAN;
+        if (it < 0) {
+          s.cur_ll[c] = new_ll;                // initial state
+        } else {
+          double old_ll = s.cur_ll[c];
+          const bool acc = (bad == 0) && mh_accepts(new_ll, old_ll, mh_uniform(md, s.uu, it, c));
+          if (acc) {
+            for (int p = 0; p < md.P; ++p) cur[p] = prop[p];
+            old_ll = new_ll;
+          }
+          s.cur_ll[c] = old_ll;
+          write_row(md, row, cur, s.beta + (size_t)c * 3, old_ll, acc ? 1.0 : 0.0);
+        }
+      }
+    }
+    alive = s.dead[c] ? 0 : 1;
+    info[c] = 0;                               // scheduler state of the next launch: info, ...
+  }
+  __syncthreads();
+  // ... progress counters and pre-accumulation flags of this chain, the ticket and the per-SM pause state
+  for (int i = tid; i < g.rt; i += blockDim.x) done[(size_t)c * g.rt + i] = 0;
+  for (int i = tid; i < g.nt; i += blockDim.x) done[(size_t)g.batch * g.rt + (size_t)c * g.nt + i] = 0;
+  if (c == 0) {
+    if (tid == 0) sched->next_task = 0;
+    for (int e = tid; e < SCHED_MAXSM; e += blockDim.x) { sched->smslot[e] = 0; sched->pause[2 * e] = 0; sched->pause[2 * e + 1] = 0; }
+  }
+  if (!propose_next || !alive) return;
+  // the next proposal: one lane per parameter (SimulatedGp.scala:118-127), then the hyper-parameters
+  if (tid < md.P) {
+    const double v = cur[tid] * exp(md.delta * mh_normal(md, s.z, it + 1, c, tid));
+    prop[tid] = v; sprop[tid] = v;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    Hyper h;
+    fill_hyper_dev(md, sprop, s.beta + (size_t)c * 3, md.nbeta, h);
+    hyper[c] = h;
+  }
+}
+
 // ---- one-launch path for n <= 64 ------------------------------------------------------------------
 // One CTA per chain walks `count` iterations: proposal, covariance (the reference's exact operation
 // order), left-looking Cholesky with the rhs row bordered below the matrix (u = L^-1 r falls out of the
@@ -263,11 +345,6 @@ struct TinySmem {
   Hyper h;
   int info;
 };
-__device__ __forceinline__ double warp_sum_d(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
 // Log-likelihood reductions of the system for sm.h (info in sm.info); every thread returns them.
 // blockDim.x = the n + 1 stacked rows rounded up to whole warps: at n = 20 every barrier is one warp.
 __device__ void tiny_eval(const MhDev& md, TinySmem& sm, double& Q, double& U1, double& S) {
@@ -639,12 +716,23 @@ int gpb_mh_run_ex(gpb_ctx* ctx, const gpb_dataset* ds, const gpb_mh_config* cfg_
           k_mh_gibbs<<<gb, tb, 0, st>>>(md, s, it, ctx->info);
           ctx->launches += 2;
         }
+        double* rows_it = it >= 0 ? ring[b] + (size_t)(it - it0) * cpad * md.RW : nullptr;
+        if (d == 0) {
+          // fixed mean: k_build -> k_chol_tasks -> k_mh_step (reductions + accept + next proposal + reset)
+          if (it < 0) { k_mh_propose<<<gb, tb, 0, st>>>(md, s, it, ctx->hyper); ctx->launches += 1; }
+          launch_build(st, g_ll, ds->x, ds->y, nullptr, ctx->hyper, cfg.nugget, ctx->mats, BUILD_FAST, 0);
+          if ((rc = do_chol(ctx, g_ll, 0, it >= 0 ? 1 : 0))) return rc;
+          k_mh_step<<<chains, 256, 0, st>>>(md, s, g_ll, it, it + 1 < iters ? 1 : 0, ctx->mats, ctx->info, ctx->done,
+                                            ctx->sched, ctx->hyper, rows_it);
+          ctx->launches += 2;
+          continue;
+        }
         k_mh_propose<<<gb, tb, 0, st>>>(md, s, it, ctx->hyper);
         launch_build(st, g_ll, ds->x, ds->y, nullptr, ctx->hyper, cfg.nugget, ctx->mats, BUILD_FAST, 0);
         ctx->launches += 2;
         if ((rc = do_chol(ctx, g_ll, 0))) return rc;
         launch_ll_epilogue(st, g_ll, ctx->mats, ctx->info, ctx->ll);
-        k_mh_accept<<<gb, tb, 0, st>>>(md, s, it, ctx->ll, it >= 0 ? ring[b] + (size_t)(it - it0) * cpad * md.RW : nullptr);
+        k_mh_accept<<<gb, tb, 0, st>>>(md, s, it, ctx->ll, rows_it);
         ctx->launches += 2;
       }
     }

@@ -25,7 +25,7 @@ EXPORTS = [
     "gpb_plane_stats", "gpb_sample_plane", "gpb_draw", "gpb_mll_gradient",
     "gpb_schedule_task", "gpb_build_cov_hot", "gpb_mh_run_ex", "gpb_mh_run_host", "gpb_philox_streams_device",
     "gpb_comm_unique_id", "gpb_comm_init_rank", "gpb_comm_init_all", "gpb_comm_destroy", "gpb_comm_info",
-    "gpb_comm_shard", "gpb_gather",
+    "gpb_comm_shard", "gpb_gather", "gpb_loglik_noalloc",
 ]
 RNG_HOST, RNG_PHILOX = 0, 1
 SMALL_AUTO, SMALL_OFF = 0, 1
@@ -122,6 +122,8 @@ def load():
                                    C.c_int, C.c_double, C.POINTER(LL)]
     L.gpb_loglik.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, _dp, C.c_int,
                              C.c_double, C.POINTER(LL)]
+    L.gpb_loglik_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.POINTER(Term), C.c_int, _dp, C.c_int, C.c_double, C.POINTER(LL)]
     L.gpb_predict.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Term), C.c_int, C.c_double, C.c_int,
                               _dp, _dp, _dp, _ip]
     L.gpb_distance_matrix.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp]
@@ -193,6 +195,25 @@ def terms_array(term_lists):
             arr[k] = Term(int(kind), float(p0), float(p1), 0.0)
             k += 1
     return arr, nterms
+
+
+NOALLOC_MAX_N = 512
+
+
+def loglik_noalloc(device, stream, n, dim, d_x, d_y, terms, beta=None, nugget=1e-3):
+    """gpb_loglik_noalloc: d_x / d_y are DEVICE addresses (ints) the caller owns; `stream` a cudaStream_t
+    handle (0 / None = the default stream).  Returns (status, LL); allocates nothing on the device."""
+    L = load()
+    arr, nterms = terms_array([terms])
+    if beta is None or len(beta) == 0:
+        bptr, nbeta = None, 0
+    else:
+        bv = as_f64(beta)
+        bptr, nbeta = _ptr(bv), bv.size
+    out = LL()
+    st = L.gpb_loglik_noalloc(int(device), C.c_void_p(int(stream or 0)), int(n), int(dim), C.c_void_p(int(d_x)),
+                              C.c_void_p(int(d_y)), arr, nterms, bptr, nbeta, float(nugget), C.byref(out))
+    return st, out
 
 
 class Context:

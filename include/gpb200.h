@@ -92,6 +92,26 @@ int gpb_loglik_batch(gpb_ctx *ctx, const gpb_dataset *ds, int batch, const gpb_t
  * C = n/2 log(2 pi).  NaN when info != 0. */
 double gpb_ll_value(const gpb_ll *r, int formula);
 
+/* gpb_loglik for callers that cannot allocate.  No counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc.  Same kernels and the same result (bit for bit) as gpb_loglik on the same inputs,
+ * but the call makes no cudaMalloc / cudaFree / allocating library call and needs no gpb_ctx: the
+ * factorisation's workspace is a static __device__ array inside the library, sized for
+ * n <= GPB_NOALLOC_MAX_N (2.7 MB, held by every GPU that loads the library until the process exits).
+ * A larger n is refused with GPB_E_INVALID and a message on stderr.
+ *   device      CUDA device ordinal (made current);  stream: the caller's cudaStream_t (NULL = the
+ *               default stream); the call is synchronous on return.
+ *   d_x, d_y    DEVICE pointers owned by the caller: locations SoA [dim][n], observations [n].
+ *   terms, beta, out   HOST pointers, as in gpb_loglik.
+ * All calls share the one array, which keeps the last call's contents (the call rewrites everything
+ * it reads).  Calls that overlap on the GPU race on it: the library serialises the calls a process
+ * makes through this entry point (a mutex; the call is synchronous on return), and anything that
+ * replays these kernels outside that mutex (a captured graph) must not overlap another call. */
+#define GPB_NOALLOC_MAX_N 512
+int gpb_loglik_noalloc(int device, void *stream, int n, int dim, const double *d_x, const double *d_y,
+                       const gpb_term *terms, int nterms, const double *beta, int nbeta, double nugget,
+                       gpb_ll *out);
+
 /* ---- posterior predictive ---------------------------------------------------------------- */
 /* Predict.fit(newXs, observed, dist, p)  Predict.scala:57-94 (buildDistVec :21-29).  Mirrors the
  * reference: raw y (no mean subtraction, :80), var = k(0) - u.u with k(0) including the white

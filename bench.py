@@ -189,7 +189,7 @@ def run_reference(args):
                          "sample": f"{steps_done} steps x {B} full n={N_TRAIN} evaluations, 1 thread each, {lanes} step(s) side by side on {threads} of {cores} host cores (time-bounded; reference JVM path: unavailable on this box)"},
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -311,7 +311,7 @@ def run_ours(args):
             "cpu_baseline": cpu,
             "extra": extra,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     ds.close()
     if dist is not None:
         dist.barrier()
@@ -580,7 +580,28 @@ def extras_multi_gpu(ctx, G, CH, dist, local):
     return out
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """stdout carries ONE JSON line: native libraries that write to fd 1 on their own (NCCL's version
+    banner under NCCL_DEBUG=VERSION/WARN/INFO without NCCL_DEBUG_FILE) are pointed at stderr, and the
+    line goes out through a private duplicate of the original stdout."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=None)

@@ -317,12 +317,23 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       if (tid == c + 1) { const double s1v = a1 * rs1; l1 = fma(0.5 * rs1, fma(-s1v, s1v, a1), s1v); }
       p[q] = l0; p[q + 1] = l1;
     }
+    // the panel's columns are final: back to shared memory for the trailing update, and straight out to
+    // global memory from the registers (L_jj columns from the top rows, L_jj^-T rows -- pitch LDT, the
+    // layout the TMA boxes of the solves read -- from the bottom rows), so that the stores drain behind
+    // the remaining panels instead of in front of the publication
     if (top) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) sm.Cs[(c0 + q) * LDT + rr] = p[q];
+      if (store_L) {
+#pragma unroll
+        for (int q = 0; q < PB; ++q)
+          if (rr >= c0 + q) Aij[(size_t)(c0 + q) * ld + rr] = p[q];
+      }
     } else if (act) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) wcol(sm, s0, c0 + q)[rr] = p[q];
+#pragma unroll
+      for (int q = 0; q < PB; ++q) LT[(c0 + q) * LDT + rr] = (c0 + q >= rr) ? p[q] : 0.0;
     }
     bar_named(1, NCONS);
     const int cN = c0 + PB;                        // first trailing column
@@ -352,15 +363,6 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
         }
       }
       bar_named(1, NCONS);
-    }
-  }
-  // L_jj (lower triangle) and L_jj^-T (pitch LDT, the layout the TMA boxes of the solves read) out
-  {
-    const int r = tid & (TILE - 1), half = tid >> 6;
-#pragma unroll 4
-    for (int c = half; c < TILE; c += NCONS / TILE) {
-      if (store_L && r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
-      LT[c * LDT + r] = (c >= r) ? wcol(sm, s0, c)[r] : 0.0;
     }
   }
 }

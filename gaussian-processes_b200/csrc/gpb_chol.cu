@@ -211,17 +211,9 @@ __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* erro
 }
 
 
-// 1/a and 1/sqrt(a) from the hardware approximations (2^-23) plus two Newton steps each: the
-// reciprocal sits on the per-column dependency chain of the diagonal factorisation, where the
-// IEEE division / rsqrt subroutines would triple its length.
-__device__ __forceinline__ double fast_rcp(double a) {
-  double x;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
-  double e = fma(-a, x, 1.0);
-  x = fma(x, e, x);
-  e = fma(-a, x, 1.0);
-  return fma(x, e, x);
-}
+// 1/sqrt(a) from the hardware approximation (2^-23) plus two Newton steps: the IEEE rsqrt / division
+// subroutines are several times as long (the reciprocals the elimination used to need are gone: the
+// panel of diag_factor is eliminated division-free).
 __device__ __forceinline__ double fast_rsqrt(double a) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
@@ -241,8 +233,8 @@ __device__ __forceinline__ double flip_sign(double x) {
 // stages the producer grants to the diagonal task (stage s0 + c / SCOLS holds columns c of W, pitch
 // LDT), so the kernel needs no second tile buffer.  Blocked by 16 columns:
 //   panel   : one thread per stacked row keeps its 16 panel entries in registers; right-looking
-//             inside the panel with the column left unscaled until the end of its step
-//             (row[c2] -= (v_c(r)/a) v_c(c2)), ONE named barrier per column;
+//             inside the panel, two columns per named barrier, division-free (the entries still to be
+//             eliminated carry a common factor; no reciprocal on the dependency chain, see below);
 //   trailing: rank-16 update of the remaining columns on the FP64 tensor cores, in place in
 //             shared memory.  Only 8 of the 16 row blocks are live at any step (top rows below
 //             the panel, bottom rows the panel has reached), two per warp.
@@ -280,6 +272,15 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
 #pragma unroll
       for (int q = 0; q < PB; ++q) p[q] = wcol(sm, s0, c0 + q)[rr];
     }
+    // Division-free elimination: the entries of the panel that are still to be eliminated carry a common
+    // factor `sig` (1 at the start of the panel).  Eliminating the column pair (c, c+1) with the 2 x 2 pivot
+    // block [[a0, w], [w, b1]], det = a0 b1 - w^2, as
+    //     S' = det S - (b1 v0 v0^T - w (v0 v1^T + v1 v0^T) + a0 v1 v1^T)      (= det x the Schur complement)
+    // needs no reciprocal on the dependency chain: per entry  p' = det p - x0 g0 - x1 g1  with the
+    // thread's own g0 = b1 y0 - w y1, g1 = a0 y1 - w y0.  det is normalised into [1, 2) by an exact power
+    // of two, so sig grows by less than 2 per pair.  The finished columns leave the chain as true L
+    // entries: L(r, c) = y0 / sqrt(a0 sig), L(r, c+1) = g1 / sqrt(det a0 sig)  (rsqrt off the chain).
+    double sig = 1.0;
 #pragma unroll
     for (int q = 0; q < PB; q += 2) {
       // two columns per barrier: every thread rebuilds column c+1 after the elimination of column c
@@ -289,33 +290,40 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       if (act) { cb0[tid] = p[q]; cb1[tid] = p[q + 1]; }
       bar_named(1, NCONS);
       const int c = c0 + q;
-      const double a0 = cb0[c];                    // pivot of column c (Schur complement diagonal)
+      const double a0 = cb0[c];                    // pivot of column c (x sig)
       const double w = cb0[c + 1];                 // entry (c+1, c)
+      const double b1 = cb1[c + 1];
       if (tid == c && !(a0 > 0.0) && sm.bad_col < 0) sm.bad_col = c;   // first bad column only
-      // 1/a1 = a0 / (a0 b1 - w^2): the two reciprocals do not depend on each other, which takes one
-      // whole reciprocal (5 dependent FP64 operations) off the per-pair dependency chain
-      const double det = fma(a0, cb1[c + 1], -(w * w));
-      const double r0 = fast_rcp(a0);
-      const double rd = fast_rcp(det);
-      const double gm = w * r0;
-      const double a1 = det * r0;                  // pivot of column c+1 after eliminating column c
-      if (tid == c + 1 && (a0 > 0.0) && !(a1 > 0.0) && sm.bad_col < 0) sm.bad_col = c + 1;
-      const double r1 = a0 * rd;
-      const double f0 = p[q] * r0;                 // v_c(r) / a0
-      const double p1 = fma(-f0, w, p[q + 1]);     // own entry of column c+1 after column c
-      const double f1 = p1 * r1;
+      const double det = fma(a0, b1, -(w * w));    // a0 x the pivot of column c+1 after column c
+      if (tid == c + 1 && (a0 > 0.0) && !(det > 0.0) && sm.bad_col < 0) sm.bad_col = c + 1;
+      int ex = (__double2hiint(det) >> 20) & 0x7ff;
+      ex = min(max(ex, 1), 2045);
+      const double sc = __hiloint2double((2046 - ex) << 20, 0);   // 2^-k, exact
+      const double dets = det * sc;
+      const double y0 = p[q], y1 = p[q + 1];
+      const double g0 = fma(b1, y0, -(w * y1)) * sc;
+      const double g1r = fma(a0, y1, -(w * y0));   // == det for the thread of row c+1, bit for bit
+      const double g1 = g1r * sc;
 #pragma unroll
       for (int q2 = q + 2; q2 < PB; ++q2) {
         const double x0 = cb0[c0 + q2], x1 = cb1[c0 + q2];
-        const double v1 = fma(-gm, x0, x1);        // entry (c0+q2, c+1) after column c
-        p[q2] = fma(-f1, v1, fma(-f0, x0, p[q2]));
+        p[q2] = fma(-x1, g1, fma(-x0, g0, dets * p[q2]));
       }
-      // off the chain: scaled column entries; the pivots get one more Newton step (L_cc ~0.5 ulp)
-      const double rs0 = fast_rsqrt(a0), rs1 = fast_rsqrt(a1);
-      double l0 = p[q] * rs0, l1 = p1 * rs1;
-      if (tid == c) { const double s0v = a0 * rs0; l0 = fma(0.5 * rs0, fma(-s0v, s0v, a0), s0v); }
-      if (tid == c + 1) { const double s1v = a1 * rs1; l1 = fma(0.5 * rs1, fma(-s1v, s1v, a1), s1v); }
+      // off the chain: the two finished columns; the pivots get one more Newton step (L_cc ~0.5 ulp)
+      const double as = a0 * sig;
+      const double das = det * as;
+      const double rs0 = fast_rsqrt(as), rs1 = fast_rsqrt(das);
+      double l0 = y0 * rs0, l1 = g1r * rs1;
+      if (tid == c) {                              // l0^2 sig = a0
+        const double l2 = l0 * l0, lr = fma(l0, l0, -l2);
+        l0 = fma(0.5 * rs0, fma(-lr, sig, fma(-l2, sig, a0)), l0);
+      }
+      if (tid == c + 1) {                          // l1^2 (a0 sig) = det
+        const double l2 = l1 * l1, lr = fma(l1, l1, -l2);
+        l1 = fma(0.5 * rs1, fma(-lr, as, fma(-l2, as, det)), l1);
+      }
       p[q] = l0; p[q + 1] = l1;
+      sig *= dets;
     }
     // the panel's columns are final: back to shared memory for the trailing update, and straight out to
     // global memory from the registers (L_jj columns from the top rows, L_jj^-T rows -- pitch LDT, the

@@ -211,9 +211,17 @@ __device__ __forceinline__ bool wait_counter(const int* ctr, int need, int* erro
 }
 
 
-// 1/sqrt(a) from the hardware approximation (2^-23) plus two Newton steps: the IEEE rsqrt / division
-// subroutines are several times as long (the reciprocals the elimination used to need are gone: the
-// panel of diag_factor is eliminated division-free).
+// 1/a and 1/sqrt(a) from the hardware approximations (2^-23) plus two Newton steps each: the IEEE
+// division / rsqrt subroutines are several times as long.  (The division-free panel elimination of
+// diag_factor needs no reciprocal; the range fallback keeps them on its dependency chain.)
+__device__ __forceinline__ double fast_rcp(double a) {
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+  double e = fma(-a, x, 1.0);
+  x = fma(x, e, x);
+  e = fma(-a, x, 1.0);
+  return fma(x, e, x);
+}
 __device__ __forceinline__ double fast_rsqrt(double a) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
@@ -253,8 +261,12 @@ __device__ __forceinline__ void write_L_tile(const CholSmem& sm, double* __restr
   for (int c = half; c < TILE; c += NCONS / TILE)
     if (r >= c) Aij[(size_t)c * ld + r] = sm.Cs[c * LDT + r];
 }
-__device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restrict__ Aij,
-                                         double* __restrict__ LT, int ld, int tid, bool store_L) {
+// SCALED: the block in sm.Cs has been equilibrated (diag_factor below); the global stores undo it with this
+// thread's row constants (uL for a row of L_jj, uW for a row of L_jj^-T).
+template <bool SCALED>
+__device__ __noinline__ void diag_factor_t(CholSmem& sm, int s0, double* __restrict__ Aij,
+                                           double* __restrict__ LT, int ld, int tid, bool store_L,
+                                           double uL, double uW) {
   const int warp = tid >> 5, lane = tid & 31, gq = lane >> 2, tq = lane & 3;
   // W arrives as the identity (TMA, producer warp); every thread has waited on those stages
   const bool top = tid < TILE, act = tid < 2 * TILE;   // threads beyond the 128 stacked rows only keep the barriers
@@ -335,13 +347,13 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       if (store_L) {
 #pragma unroll
         for (int q = 0; q < PB; ++q)
-          if (rr >= c0 + q) Aij[(size_t)(c0 + q) * ld + rr] = p[q];
+          if (rr >= c0 + q) Aij[(size_t)(c0 + q) * ld + rr] = SCALED ? p[q] * uL : p[q];
       }
     } else if (act) {
 #pragma unroll
       for (int q = 0; q < PB; ++q) wcol(sm, s0, c0 + q)[rr] = p[q];
 #pragma unroll
-      for (int q = 0; q < PB; ++q) LT[(c0 + q) * LDT + rr] = (c0 + q >= rr) ? p[q] : 0.0;
+      for (int q = 0; q < PB; ++q) LT[(c0 + q) * LDT + rr] = (c0 + q >= rr) ? (SCALED ? p[q] * uW : p[q]) : 0.0;
     }
     bar_named(1, NCONS);
     const int cN = c0 + PB;                        // first trailing column
@@ -373,6 +385,40 @@ __device__ __noinline__ void diag_factor(CholSmem& sm, int s0, double* __restric
       bar_named(1, NCONS);
     }
   }
+}
+
+// The division-free elimination forms products of two entries of the block (a0 b1, w^2, b1 y0, ...).  Every
+// covariance matrix of the path is hundreds of orders of magnitude away from where those overflow, but a
+// matrix-level gpb_potrf near the ends of the double range must not fail where dpotrf does not: when a
+// diagonal entry lies outside 2^-300 .. 2^300 the block is first equilibrated, D A D with D = diag(2^-k_r),
+// k_r = floor(exponent(a_rr) / 2) -- exact, and every diagonal entry lands in [1, 4); entries of an SPD
+// block are bounded by its diagonal, Schur complements only shrink it -- and the stores undo it exactly:
+// L = D^-1 L_s, L^-T = D L_s^-T, both row scalings (one constant per thread).  One reducing barrier per block
+// on the ordinary path.
+__device__ __forceinline__ void diag_factor(CholSmem& sm, int s0, double* __restrict__ Aij,
+                                            double* __restrict__ LT, int ld, int tid, bool store_L) {
+  int ex = 1023;
+  if (tid < TILE) ex = (__double2hiint(sm.Cs[tid * LDT + tid]) >> 20) & 0x7ff;   // sign bit set: not PD anyway
+  const bool in_range = ex >= 1023 - 300 && ex <= 1023 + 300;
+  if (bar_named_and(1, NCONS, in_range)) {
+    diag_factor_t<false>(sm, s0, Aij, LT, ld, tid, store_L, 1.0, 1.0);
+    return;
+  }
+  double* ks = &sm.colbuf[0][0][0];          // k_r of the 64 rows (free until the first column pair is published)
+  if (tid < TILE) {
+    const int e = min(max(ex, 1), 2046) - 1023;
+    ks[tid] = (double)((e - (e & 1)) / 2);   // floor(e / 2)
+  }
+  bar_named(1, NCONS);
+  const int kr = (int)ks[tid & (TILE - 1)];
+  if (tid < TILE)
+    for (int c = 0; c < TILE; ++c)
+      sm.Cs[c * LDT + tid] *= __hiloint2double((1023 - kr - (int)ks[c]) << 20, 0);
+  const double uL = __hiloint2double((1023 + kr) << 20, 0), uW = __hiloint2double((1023 - kr) << 20, 0);
+  bar_named(1, NCONS);
+  diag_factor_t<true>(sm, s0, Aij, LT, ld, tid, store_L, uL, uW);
+  if (tid < TILE)                            // sm.Cs keeps L_jj for write_L_tile
+    for (int c = 0; c < TILE; ++c) sm.Cs[c * LDT + tid] *= uL;
 }
 
 // Triangular-solve mode: sm.Cs holds a given lower-triangular L_jj; thread 64+k computes row k of

@@ -161,6 +161,30 @@ def test_predict_parity(ctx, oracle, n, m, dim):
     ds.close()
 
 
+@pytest.mark.parametrize("n", [64, 150, 257])
+def test_potrf_near_the_ends_of_the_double_range(ctx, oracle, n):
+    """dpotrf works wherever its square roots and quotients do; the diagonal blocks here are eliminated
+    division-free (products of two entries), so blocks outside 2^-300 .. 2^300 are rescaled by an exact even
+    power of two first: the factor of 2^(2k) K must be 2^k L, bit for bit, and an odd power must agree to
+    rounding."""
+    x, _, _ = synth(oracle, n, 2, SE_W, 4100 + n)
+    K = oracle.build_cov(x, SE_W, 1e-3)
+    L, info = ctx.potrf(K)
+    assert info == 0
+    for k in (350, -350, 480, -500):
+        Ls, info = ctx.potrf(np.ldexp(K, 2 * k))
+        assert info == 0
+        assert np.array_equal(Ls, np.ldexp(L, k)), k
+    Lodd, info = ctx.potrf(np.ldexp(K, 701))
+    assert info == 0
+    assert np.allclose(np.ldexp(Lodd, -350), math.sqrt(2.0) * L, rtol=1e-11, atol=1e-12 * np.abs(L).max())
+    # not positive definite stays a LAPACK info, whatever the scale
+    Kbad = np.ldexp(K, 800)
+    Kbad[n - 1, n - 1] = -Kbad[n - 1, n - 1]
+    _, info = ctx.potrf(Kbad)
+    assert info == n
+
+
 @pytest.mark.parametrize("n", [1, 5, 64, 100, 257])
 def test_potrf_and_triangular_solves(ctx, oracle, n):
     rng = np.random.default_rng(n)

@@ -359,28 +359,40 @@ __device__ __noinline__ void diag_factor_t(CholSmem& sm, int s0, double* __restr
     const int cN = c0 + PB;                        // first trailing column
     if (cN < TILE) {
       // M(R, c2) -= sum_q P(R, q) P(c2, q)  for c2 >= cN;  D[m = c2][n = R], k = q
-#pragma unroll 1
-      for (int h = 0; h < 8 / CW; ++h) {
-        const int blk = (8 / CW) * warp + h;       // live row block 0..7
-        const int ntop = (TILE - cN) / 8;          // live top blocks: rows cN .. 63
-        const bool btop = blk < ntop;
-        const int r0 = btop ? cN + 8 * blk : 8 * (blk - ntop);
-        double bf[PB / 4];
+      // the warp's row blocks side by side: they share the panel-column operand, and their DMMA chains
+      // (4 k-steps each) are independent
+      constexpr int NH = 8 / CW;
+      const int ntop = (TILE - cN) / 8;            // live top blocks: rows cN .. 63
+      bool btop[NH]; int r0[NH]; double bf[NH][PB / 4];
+#pragma unroll
+      for (int h = 0; h < NH; ++h) {
+        const int blk = NH * warp + h;             // live row block 0..7
+        btop[h] = blk < ntop;
+        r0[h] = btop[h] ? cN + 8 * blk : 8 * (blk - ntop);
 #pragma unroll
         for (int ks = 0; ks < PB / 4; ++ks) {
           const int c = c0 + ks * 4 + tq;
-          bf[ks] = btop ? sm.Cs[c * LDT + r0 + gq] : wcol(sm, s0, c)[r0 + gq];
+          bf[h][ks] = btop[h] ? sm.Cs[c * LDT + r0[h] + gq] : wcol(sm, s0, c)[r0[h] + gq];
         }
+      }
 #pragma unroll 2
-        for (int c2 = cN; c2 < TILE; c2 += 8) {
-          double* col = btop ? &sm.Cs[(c2 + gq) * LDT] : wcol(sm, s0, c2) + gq * LDT;
-          double2* dp = reinterpret_cast<double2*>(&col[r0 + 2 * tq]);
-          double2 dv = *dp;
+      for (int c2 = cN; c2 < TILE; c2 += 8) {
+        double a[PB / 4];
 #pragma unroll
-          for (int ks = 0; ks < PB / 4; ++ks)
-            dmma884(dv.x, dv.y, -sm.Cs[(c0 + ks * 4 + tq) * LDT + c2 + gq], bf[ks]);
-          *dp = dv;
+        for (int ks = 0; ks < PB / 4; ++ks) a[ks] = -sm.Cs[(c0 + ks * 4 + tq) * LDT + c2 + gq];
+        double2* dp[NH]; double2 dv[NH];
+#pragma unroll
+        for (int h = 0; h < NH; ++h) {
+          double* col = btop[h] ? &sm.Cs[(c2 + gq) * LDT] : wcol(sm, s0, c2) + gq * LDT;
+          dp[h] = reinterpret_cast<double2*>(&col[r0[h] + 2 * tq]);
+          dv[h] = *dp[h];
         }
+#pragma unroll
+        for (int ks = 0; ks < PB / 4; ++ks)
+#pragma unroll
+          for (int h = 0; h < NH; ++h) dmma884(dv[h].x, dv[h].y, a[ks], bf[h][ks]);
+#pragma unroll
+        for (int h = 0; h < NH; ++h) *dp[h] = dv[h];
       }
       bar_named(1, NCONS);
     }

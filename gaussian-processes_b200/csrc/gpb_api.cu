@@ -42,7 +42,7 @@ int ensure_workspace(gpb_ctx* ctx, const Geom& g) {
   int rc;
   if ((rc = grow(ctx, &ctx->mats, &ctx->mats_doubles, g.mat_stride * g.batch))) return rc;
   if ((rc = grow(ctx, &ctx->linvt, &ctx->linvt_doubles, chol_linvt_doubles(g)))) return rc;
-  if ((rc = grow(ctx, &ctx->done, &ctx->done_ints, (size_t)g.batch * (g.rt + g.nt)))) return rc;
+  if ((rc = grow(ctx, &ctx->done, &ctx->done_ints, chol_done_ints(g)))) return rc;
   if ((rc = grow(ctx, &ctx->info, &ctx->info_ints, (size_t)g.batch))) return rc;
   if ((rc = grow(ctx, &ctx->hyper, &ctx->hyper_n, (size_t)g.batch))) return rc;
   if ((rc = grow(ctx, &ctx->ll, &ctx->ll_n, (size_t)g.batch))) return rc;

@@ -85,6 +85,12 @@ struct __align__(128) CholSmem {
   int taskq[2];
   int4 taskd[2];                        // the decoded ticket (b, i, j, kind): consumers do not decode again
   int bad_col;
+  // early hand-over of the first half of L_jj^-T (chain-bound instantiation): request set by the caller of
+  // diag_factor, one-slot channel to the producer lane's release service
+  int* hf_req;
+  int* hf_ptr;
+  int hf_count;
+  uint64_t hf_full, hf_empty;
   int* pause_mine;                      // chain_pause: this CTA's "inside a critical section" flag ...
   int* pause_other;                     // ... and the flag of the CTA it shares the SM with
 };
@@ -176,7 +182,7 @@ __device__ __forceinline__ int task_k0(const Geom& g, const TaskDesc& d) {
 // an appended identity block.
 __global__ void k_chol_reset(Geom g, int* __restrict__ done, int* __restrict__ info, SchedState* sched,
                              double* __restrict__ linvt) {
-  const int per = g.rt + g.nt;               // done [batch][rt] followed by part [batch][nt]
+  const int per = g.rt + 2 * g.nt;           // done [batch][rt], then part [batch][nt], then half [batch][nt]
   const long long total = (long long)g.batch * per;
   // the identity tile behind the L_jj^-T tiles (the workspace may have moved since the last launch)
   double* ident = linvt + (size_t)g.batch * g.nt * TILE * LDT;
@@ -355,8 +361,18 @@ __device__ __noinline__ void diag_factor_t(CholSmem& sm, int s0, double* __restr
 #pragma unroll
       for (int q = 0; q < PB; ++q) LT[(c0 + q) * LDT + rr] = (c0 + q >= rr) ? (SCALED ? p[q] * uW : p[q]) : 0.0;
     }
-    bar_named(1, NCONS);
     const int cN = c0 + PB;                        // first trailing column
+    // rows 0..31 of L_jj^-T (the first stage of the solves that wait for this block) are final after the
+    // second panel: published on the way when the caller asked for it (sm.hf_req)
+    const bool early = (cN == SCOLS) && (tid == 0) && (sm.hf_req != nullptr);
+    int hfn = 0;
+    if (early) {
+      hfn = sm.hf_count;
+      (void)mbar_wait(&sm.hf_empty, (hfn & 1) ^ 1);   // bounded; the producer lane serves the slot within a microsecond
+      sm.hf_ptr = sm.hf_req;
+    }
+    bar_named(1, NCONS);                           // the panel is in shared memory; its global stores are ordered before the post
+    if (early) { mbar_arrive(&sm.hf_full); sm.hf_count = hfn + 1; }
     if (cN < TILE) {
       // M(R, c2) -= sum_q P(R, q) P(c2, q)  for c2 >= cN;  D[m = c2][n = R], k = q
       // the warp's row blocks side by side: they share the panel-column operand, and their DMMA chains
@@ -568,8 +584,16 @@ __device__ __noinline__ void syrk_task(CholSmem& sm, double* __restrict__ Aij, i
 // the consumers' stores, ordered before it by the CTA barrier + mbarrier), proxy fence (the
 // readers are TMA loads), release store.  Every producer spin loop calls this, so a pending
 // publication can never be starved.
-struct RelState { int r; };
+struct RelState { int r; int h; };
 __device__ __forceinline__ void service_release(CholSmem& sm, RelState& rs) {
+  if (mbar_test_wait(&sm.hf_full, rs.h & 1)) {     // early half of L_jj^-T (see diag_factor_t)
+    int* p = sm.hf_ptr;
+    __threadfence();
+    fence_proxy_async();
+    st_release(p, 1);
+    mbar_arrive(&sm.hf_empty);
+    ++rs.h;
+  }
   for (;;) {
     const int slot = rs.r & 1, par = (rs.r >> 1) & 1;
     if (!mbar_test_wait(&sm.rel_full[slot], par)) return;
@@ -606,6 +630,24 @@ __device__ __forceinline__ int wait_counter_serving(const int* ctr, int need, in
   }
 }
 
+// Wait for the first half of L_jj^-T (rows 0..31: the running factorisation raises `half` behind its second
+// panel) or, with first == false, for the whole block (the row's progress counter).  Returns 1 when the
+// block is complete, 0 when only its first half is, -1 on error / watchdog.
+__device__ __forceinline__ int wait_lt_serving(const int* half, bool first, const int* donej, int need, int* error,
+                                               CholSmem& sm, RelState& rs) {
+  long long t0 = 0;
+  for (int spin = 0;; ++spin) {
+    if (ld_acquire(donej) >= need) return 1;
+    if (first && ld_acquire(half) >= 1) return 0;
+    if (spin == 0) t0 = clock64();
+    service_release(sm, rs);
+    if ((spin & 15) == 15) {
+      if (*(volatile int*)error) return -1;
+      if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(error, 1); return -1; }
+    }
+  }
+}
+
 // TRACE = true is the schedule-analysis build of the same kernel (gpb_set_trace); the production
 // instantiation carries no timestamp code or registers.
 // MINB = CTAs per SM the register budget is sized for: 2 (168 registers) for throughput launches, 1
@@ -620,6 +662,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   constexpr bool DIRECT_DIAG = (MINB == 1);   // chain-bound instantiation (in throughput mode it makes no difference: measured)
+  // chain-bound instantiation: the first half of L_jj^-T is handed over while the factorisation still runs
+  constexpr bool EARLY_HALF = (MINB == 1);
 
   if (tid == 0) {
     tma_prefetch_desc(&tmap);
@@ -627,6 +671,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     for (int s = 0; s < STAGES; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.tq_full[s], 1); mbar_init(&sm.tq_empty[s], NCONS / 32); }
     for (int s = 0; s < 2; ++s) { mbar_init(&sm.rel_full[s], 1); mbar_init(&sm.rel_empty[s], 1); }
+    mbar_init(&sm.hf_full, 1); mbar_init(&sm.hf_empty, 1);
+    sm.hf_req = nullptr; sm.hf_ptr = nullptr; sm.hf_count = 0;
     mbar_fence_init();
     sm.pause_mine = sm.pause_other = nullptr;
     if (MINB == 2 && chain_pause) {   // the one-CTA-per-SM instantiation has no neighbour to pause
@@ -645,7 +691,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
   if (warp == NCONS / 32) {
     // =============================== producer warp ===============================
     int q = 0, static_next = task_begin + blockIdx.x;
-    RelState rs; rs.r = 0;
+    RelState rs; rs.r = 0; rs.h = 0;
+    int posted_h = 0; // early halves the consumers will post
     int posted = 0;   // tasks handed to the consumers that will post a publication
     // The next ticket is drawn when every load of the current task has been issued (its last stages
     // are still in flight then, so the atomic's latency stays hidden).  The later, the better for
@@ -700,6 +747,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       // (the chain-bound instantiation publishes diagonal blocks itself, see factor_block)
       if (!solve_only) posted += (DIRECT_DIAG) ? ((kind == K_FUSED || kind == K_PART || (kind == K_PLAIN && d.i != d.j)) ? 1 : 0)
                                              : ((kind == K_FUSED) ? 2 : 1);
+      if (EARLY_HALF && !solve_only && (kind == K_FUSED || kind == K_DIAG0)) posted_h += 1;
       const int kend = (kind == K_PART) ? d.j - 1 : d.j;   // K_PART leaves the last block column to K_FUSED
       const int* done_b = done + (size_t)d.b * g.rt;
       const int* part_b = done + (size_t)g.batch * g.rt + (size_t)d.b * g.nt;
@@ -758,11 +806,26 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         } else if (d.i != d.j) {
           // the solve X = C L_jj^-T streams L_jj^-T (pitch LDT in global memory) through the same
           // ring: LT_STAGES stages of SCOLS rows each, as soon as diag(j) is published
-          if (seen_j < d.j + 1) wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
-          fence_proxy_async();
           const int row0 = (d.b * g.nt + d.j) * TILE;
+          int whole = 1;
+          if constexpr (EARLY_HALF) {
+            whole = (seen_j >= d.j + 1) ? 1 : 0;
+          } else {
+            if (seen_j < d.j + 1) wait_counter_serving(done_b + d.j, d.j + 1, &sched->error, sm, rs);
+            fence_proxy_async();
+          }
 #pragma unroll 1
           for (int s = 0; s < LT_STAGES; ++s) {
+            if constexpr (EARLY_HALF) {
+              // stage 0 (rows 0..31) goes out as soon as the running factorisation has released its first half
+              if (whole == 0) {
+                whole = wait_lt_serving(done + (size_t)g.batch * (g.rt + g.nt) + (size_t)d.b * g.nt + d.j, s == 0,
+                                        done_b + d.j, d.j + 1, &sched->error, sm, rs);
+                fence_proxy_async();
+              } else if (s == 0) {
+                fence_proxy_async();
+              }
+            }
             if (!mbar_wait_serving(&sm.empty[stage], phase ^ 1, sm, rs)) atomicExch(&sched->error, 3);
             mbar_arrive_expect_tx(&sm.full[stage], STAGE_TX_BYTES);
             tma_load_2d(&sm.stage[stage][0], &tmapL, 0, row0 + s * SCOLS, &sm.full[stage]);
@@ -801,7 +864,7 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
     if (lane == 0) {
       // drain: every task this CTA took must be published before the producer leaves
       const long long t0 = clock64();
-      while (rs.r < posted) {
+      while (rs.r < posted || rs.h < posted_h) {
         service_release(sm, rs);
         if (clock64() - t0 > WATCHDOG_CLOCKS) { atomicExch(&sched->error, 6); break; }
       }
@@ -1095,6 +1158,9 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       for (int s = 0; s < LT_STAGES; ++s) {
         wait_full(stage, phase);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if constexpr (EARLY_HALF) {
+        if (tid == 0) sm.hf_req = done + (size_t)g.batch * (g.rt + g.nt) + (size_t)d.b * g.nt + dj;   // read behind diag_factor's first barrier
       }
       diag_factor(sm, s0, Ajj, LTj, g.ld, tid, !DIRECT_DIAG);
       bar_named(1, NCONS);             // bad_col is final; every read of the scratch stages is done
@@ -1424,6 +1490,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     cudaFuncSetAttribute(k_chol_tasks<false, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cudaFuncSetAttribute(k_chol_tasks<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cudaFuncSetAttribute(k_chol_tasks<true, GPB_MINBLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
+    cudaFuncSetAttribute(k_chol_tasks<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem));
     cc.dev = dev;
     for (Entry& e : cc.e) e.mats = nullptr;
   }
@@ -1448,7 +1515,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
   if (total > 0x7fff0000LL) return -2;
   int launches = 0;
   if (!skip_reset || mode != 0) {
-    const long long total = (long long)g.batch * (g.rt + g.nt);
+    const long long total = (long long)chol_done_ints(g);
     const int blocks = (int)((total + 255) / 256 < 296 ? (total + 255) / 256 : 296);
     k_chol_reset<<<blocks, 256, 0, st>>>(g, done, info, sched, linvt);
     ++launches;
@@ -1480,7 +1547,10 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     if (chain_pause >= 0) pause = chain_pause;
     if (env_pause >= 0) pause = env_pause;
     if (ctas != 2 || num_sms > SCHED_MAXSM) pause = 0;
-    if (trace)
+    if (trace && ctas == 1)   // the schedule trace runs the instantiation the untraced launch would
+      k_chol_tasks<true, 1><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
+                                                                      (int)total, 0, solve_only, trace, 0);
+    else if (trace)
       k_chol_tasks<true, GPB_MINBLOCKS><<<grid, NTHREADS, sizeof(CholSmem), st>>>(tmap, tmapL, g, mats, linvt, done, info, sched, 0,
                                                                                   (int)total, 0, solve_only, trace, pause);
     else if (ctas == 1)

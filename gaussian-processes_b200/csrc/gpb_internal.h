@@ -26,7 +26,9 @@ void launch_build(cudaStream_t st, const Geom& g, const double* x, const double*
 
 // Tile Cholesky + panel solves of the tall system (gpb_chol.cu).
 //   done   [batch][rt]  per tile-row progress counters (tiles (i, 0..done-1) are final), followed by
-//          [batch][nt]  flags "diagonal block pre-accumulated over all but its last block column"
+//          [batch][nt]  flags "diagonal block pre-accumulated over all but its last block column" and
+//          [batch][nt]  flags "rows 0..31 of L_jj^-T published by the running factorisation"
+//          (chol_done_ints(g) ints in all)
 //   linvt  [batch][nt][TILE][LDT]  inverse-transposes of the diagonal blocks (side output, pitch LDT)
 //   info   [batch]      first non-positive pivot (1-based, LAPACK) or 0
 // mode 0: one persistent launch over all tasks; mode 1: two launches per block column.
@@ -36,6 +38,7 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
                 unsigned long long* trace = nullptr, int chain_pause = -1, int skip_reset = 0);
 // skip_reset: the caller has already zeroed the scheduler state of this launch (the MH loop's step kernel
 // does it for the next iteration: one launch less per iteration)
+inline size_t chol_done_ints(const Geom& g) { return (size_t)g.batch * (g.rt + 2 * g.nt); }
 constexpr int CHOL_TRACE_SLOTS = 14;
 long long chol_task_count(const Geom& g);
 // ticket -> {proposal, tile row, tile column, kind}; returns the number of tickets

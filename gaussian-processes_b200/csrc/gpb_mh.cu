@@ -310,7 +310,10 @@ k_mh_step(MhDev md, MhState s, Geom g, int it, int propose_next, const double* _
   __syncthreads();
   // ... progress counters and pre-accumulation flags of this chain, the ticket and the per-SM pause state
   for (int i = tid; i < g.rt; i += blockDim.x) done[(size_t)c * g.rt + i] = 0;
-  for (int i = tid; i < g.nt; i += blockDim.x) done[(size_t)g.batch * g.rt + (size_t)c * g.nt + i] = 0;
+  for (int i = tid; i < g.nt; i += blockDim.x) {
+    done[(size_t)g.batch * g.rt + (size_t)c * g.nt + i] = 0;
+    done[(size_t)g.batch * (g.rt + g.nt) + (size_t)c * g.nt + i] = 0;
+  }
   if (c == 0) {
     if (tid == 0) sched->next_task = 0;
     for (int e = tid; e < SCHED_MAXSM; e += blockDim.x) { sched->smslot[e] = 0; sched->pause[2 * e] = 0; sched->pause[2 * e + 1] = 0; }

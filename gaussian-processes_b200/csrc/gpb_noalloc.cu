@@ -31,7 +31,7 @@ constexpr int NA_LD = NA_NPAD + TILE;                       // one appended tile
 constexpr size_t align32(size_t doubles) { return (doubles + 31) / 32 * 32; }   // 256-byte sub-buffers
 constexpr size_t NA_MATS = align32((size_t)NA_LD * NA_NPAD);
 constexpr size_t NA_LINVT = align32(((size_t)NA_NPAD / TILE + 1) * TILE * LDT);
-constexpr size_t NA_DONE = align32((2 * (size_t)NA_NPAD / TILE + 1 + 1) / 2);   // (rt + nt) ints
+constexpr size_t NA_DONE = align32((3 * (size_t)NA_NPAD / TILE + 1 + 1) / 2);   // chol_done_ints: (rt + 2 nt) ints
 constexpr size_t NA_INFO = 32;
 constexpr size_t NA_SCHED = align32((sizeof(SchedState) + 7) / 8);
 constexpr size_t NA_HYPER = align32((sizeof(Hyper) + 7) / 8);

@@ -40,6 +40,11 @@ object Gpb200 {
   private val dsDestroy = fn("gpb_dataset_destroy", FunctionDescriptor.ofVoid(ADDRESS))
   private val loglik = fn("gpb_loglik", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
     JAVA_INT, ADDRESS, JAVA_INT, JAVA_DOUBLE, ADDRESS))
+  // gpb_loglik_noalloc(device, stream, n, dim, d_x, d_y, terms, nterms, beta, nbeta, nugget, out): the same
+  // evaluation for callers that may not allocate (static device scratch, n <= 512); d_x / d_y are DEVICE
+  // addresses the caller owns (e.g. from its own CUDA binding) -- no counterpart in the reference
+  private val loglikNoAlloc = fn("gpb_loglik_noalloc", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS, JAVA_INT,
+    JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT, ADDRESS, JAVA_INT, JAVA_DOUBLE, ADDRESS))
   private val llValue = fn("gpb_ll_value", FunctionDescriptor.of(JAVA_DOUBLE, ADDRESS, JAVA_INT))
   private val predict = fn("gpb_predict", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
     JAVA_INT, JAVA_DOUBLE, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS))

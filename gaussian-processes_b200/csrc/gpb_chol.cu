@@ -65,7 +65,7 @@ constexpr int AT_STAGES = TILE / SCOLS;  // stages that carry the task's own til
 static_assert(SCOLS == 32 && AT_STAGES == 2, "each consumer warp's 32 columns of the tile sit in one stage");
 static_assert(STAGES >= AT_STAGES + 2, "ring too small");
 constexpr uint32_t STAGE_TX_BYTES = 2 * KC * LDT * sizeof(double);  // two {LDT x KC} TMA boxes
-constexpr int TRACE_SLOTS = 14;   // == CHOL_TRACE_SLOTS
+constexpr int TRACE_SLOTS = 16;   // == CHOL_TRACE_SLOTS
 constexpr long long WATCHDOG_CLOCKS = 4000000000LL;  // ~2 s at 1.9 GHz
 #ifndef GPB_PAUSE_TASKS_PER_SM
 #define GPB_PAUSE_TASKS_PER_SM 48
@@ -116,7 +116,8 @@ struct TaskDesc { int b, i, j, kind; };
 // [4] dependency on the diagonal block satisfied, [5] factor / solve done, [6] clock at release,
 // [7] globaltimer at release, [8] main-loop stages that were not ready at first probe, [9] cycles the main loop spent blocked on stage data.
 // Producer lane (same SM, same clock): [10] ticket posted, [11] the task's own tile issued, [12] last
-// contraction stage issued, [13] L_jj^-T stages issued (or scratch granted).
+// contraction stage issued, [13] L_jj^-T stages issued (or scratch granted).  [14] / [15] clock before / behind the
+// factorisation of a diagonal block (diagonal and fused tasks).
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long v;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
@@ -1162,7 +1163,9 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
       if constexpr (EARLY_HALF) {
         if (tid == 0) sm.hf_req = done + (size_t)g.batch * (g.rt + g.nt) + (size_t)d.b * g.nt + dj;   // read behind diag_factor's first barrier
       }
+      if (tr) tr[14] = clock64();
       diag_factor(sm, s0, Ajj, LTj, g.ld, tid, !DIRECT_DIAG);
+      if (tr) tr[15] = clock64();
       bar_named(1, NCONS);             // bad_col is final; every read of the scratch stages is done
       if (tid == 0 && sm.bad_col >= 0) atomicCAS(&info[d.b], 0, dj * TILE + sm.bad_col + 1);  // 1-based pivot
       if (DIRECT_DIAG) {

@@ -39,7 +39,7 @@ int launch_chol(cudaStream_t st, const Geom& g, double* mats, double* linvt, int
 // skip_reset: the caller has already zeroed the scheduler state of this launch (the MH loop's step kernel
 // does it for the next iteration: one launch less per iteration)
 inline size_t chol_done_ints(const Geom& g) { return (size_t)g.batch * (g.rt + 2 * g.nt); }
-constexpr int CHOL_TRACE_SLOTS = 14;
+constexpr int CHOL_TRACE_SLOTS = 16;
 long long chol_task_count(const Geom& g);
 // ticket -> {proposal, tile row, tile column, kind}; returns the number of tickets
 long long chol_schedule_task(const Geom& g, long long ticket, int* out4);

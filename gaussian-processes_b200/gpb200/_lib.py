@@ -253,9 +253,9 @@ class Context:
         self._check(self.L.gpb_set_trace(self.h, int(on)))
 
     def get_trace(self):
-        """(tasks, 14) uint64 schedule trace of the last factorisation (see gpb200.h)."""
+        """(tasks, 16) uint64 schedule trace of the last factorisation (see gpb200.h)."""
         n = int(self.L.gpb_get_trace(self.h, None, 0))
-        out = np.zeros((n, 14), dtype=np.uint64)
+        out = np.zeros((n, 16), dtype=np.uint64)
         if n:
             self.L.gpb_get_trace(self.h, out.ctypes.data_as(C.c_void_p), n)
         return out

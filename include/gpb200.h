@@ -341,9 +341,9 @@ int gpb_last_timing(const gpb_ctx *ctx, float *t3);
 /* Scheduler selection: 0 = persistent task-graph kernel (default), 1 = one launch per block
  * column (debug / fallback on the same device code).  */
 int gpb_set_sched(gpb_ctx *ctx, int mode);
-/* Schedule analysis (profiling aid): when enabled, the factorisation kernel records 14 u64 per task
+/* Schedule analysis (profiling aid): when enabled, the factorisation kernel records 16 u64 per task
  * (timestamps of receipt / first data / contraction done / dependency satisfied / factor-or-solve
- * done / release, and the SM id).  gpb_get_trace copies up to max_tasks records of the last call
+ * done / release, the producer lane's issue times, start / end of a diagonal factorisation).  gpb_get_trace copies up to max_tasks records of the last call
  * and returns the number of tasks of that call. */
 int gpb_set_trace(gpb_ctx *ctx, int enable);
 long long gpb_get_trace(gpb_ctx *ctx, unsigned long long *out, long long max_tasks);

@@ -1,6 +1,7 @@
+"""Where a block column of the chain goes (fused tasks of one launch): solve, X X^T, factorisation, publication."""
 import sys, os, math
 import numpy as np
-ROOT = "/root/repo"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "gaussian-processes_b200")); sys.path.insert(0, os.path.join(ROOT, "tools"))
 import trace_analyze as TA
 from gpb200 import _lib as G
@@ -19,5 +20,5 @@ fused = (dec[:, 1] == dec[:, 2] + 1) & (dec[:, 1] < nt)
 us = lambda a: a / 1965.0
 t = tr[fused]
 print("fused tasks", fused.sum())
-for name, a, b in (("L^-T arrived -> solve done", 4, 5), ("solve done -> factor start (X->Cs, XX^T, barriers)", 5, 8), ("diag_factor", 8, 9), ("factor end -> release (publish, L write)", 9, 6)):
+for name, a, b in (("L^-T arrived -> solve done", 4, 5), ("solve done -> factor start (X->Cs, XX^T, barriers)", 5, 14), ("diag_factor", 14, 15), ("factor end -> release (publish, L write)", 15, 6)):
     d = us(t[:, b] - t[:, a]); print(f"  {name}: p50 {np.median(d):.2f} mean {d.mean():.2f} min {d.min():.2f}")

@@ -673,3 +673,32 @@ def test_light_rhs_row_tasks_change_nothing():
         outs.append(json.loads(line[len("RESULT"):]))
     assert outs[0] == outs[1]
     assert all(rec[0][3] == 0 for rec in outs[0])
+
+
+@pytest.mark.parametrize("n,batch", [(300, 2), (1024, 1), (640, 48)])
+def test_schedule_trace_build_gives_the_same_results(ctx, n, batch):
+    """gpb_set_trace switches to the schedule-analysis instantiations of the factorisation kernel (one per
+    launch mode: one / two CTAs per SM).  Same code apart from the timestamps: the reductions must not move
+    by a bit, every task must have left a record, and its clocks must be ordered."""
+    rng = np.random.default_rng(n + batch)
+    x = rng.uniform(-10, 10, size=(n, 2))
+    y = 1.5 * rng.standard_normal(n)
+    ds = ctx.dataset(x, y)
+    props = [[(0, 3.0 * math.exp(0.05 * rng.standard_normal()), 5.5), (1, 0.5, 0.0)] for _ in range(batch)]
+    plain = [(r.Q, r.U1, r.S, r.info) for r in ds.loglik_batch(props)]
+    ctx.set_trace(1)
+    try:
+        traced = [(r.Q, r.U1, r.S, r.info) for r in ds.loglik_batch(props)]
+        tr = ctx.get_trace().astype(np.int64)
+    finally:
+        ctx.set_trace(0)
+    ds.close()
+    assert traced == plain
+    nt = (n + 63) // 64
+    assert tr.shape == (batch * (nt * (nt + 1) - nt * (nt - 1) // 2), 16)
+    ran = tr[:, 6] > 0                                   # void tasks (nothing to pre-accumulate) leave no release time
+    assert ran.sum() >= batch * (nt * (nt + 1) // 2 + nt - 1)
+    t = tr[ran]
+    assert np.all(t[:, 6] >= t[:, 1]) and np.all(t[:, 7] >= t[:, 0])
+    fact = t[:, 15] > 0                                  # tasks that factored a diagonal block
+    assert fact.sum() == batch * nt and np.all(t[fact, 15] > t[fact, 14])

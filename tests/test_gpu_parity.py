@@ -702,3 +702,21 @@ def test_schedule_trace_build_gives_the_same_results(ctx, n, batch):
     assert np.all(t[:, 6] >= t[:, 1]) and np.all(t[:, 7] >= t[:, 0])
     fact = t[:, 15] > 0                                  # tasks that factored a diagonal block
     assert fact.sum() == batch * nt and np.all(t[fact, 15] > t[fact, 14])
+
+
+@pytest.mark.parametrize("scale", [1e200, 1e-200])
+def test_loglik_with_amplitudes_near_the_ends_of_the_double_range(ctx, oracle, scale):
+    """The whole likelihood path (hot-path build, factorisation with the equilibrated diagonal blocks, bordered
+    solve, reductions) at kernel amplitudes where products of two covariance entries leave the double range."""
+    n = 200
+    rng = np.random.default_rng(77)
+    x = rng.uniform(-10, 10, size=(n, 2))
+    y = rng.standard_normal(n)
+    terms = [("se", 3.0 * scale, 5.5), ("white", 0.5 * scale)]
+    ds = ctx.dataset(x, y)
+    r = ds.loglik_batch([gterms(terms)], nugget=0.0)[0]
+    ro = oracle.loglik(x, y, terms, nugget=0.0)
+    ds.close()
+    assert r.info == 0 and ro["info"] == 0
+    for got, want in ((r.Q, ro["Q"]), (r.U1, ro["U1"]), (r.S, ro["S"])):
+        assert rel(got, want) < LL_RTOL, (scale, got, want)

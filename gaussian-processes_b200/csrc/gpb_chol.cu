@@ -662,9 +662,14 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   CholSmem& sm = *reinterpret_cast<CholSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  constexpr bool DIRECT_DIAG = (MINB == 1);   // chain-bound instantiation (in throughput mode it makes no difference: measured)
-  // chain-bound instantiation: the first half of L_jj^-T is handed over while the factorisation still runs
-  constexpr bool EARLY_HALF = (MINB == 1);
+  // The features that shorten the chain diag(j) -> (j+1, j) -> diag(j+1) -- direct publication of a factored
+  // block by consumer thread 0, the first half of L_jj^-T handed over while the factorisation still runs, the
+  // X X^T update of the fused task as a balanced SYRK -- were specific to the chain-bound instantiation until
+  // the end of round 2.  Re-measured together on the final kernels they also pay in the throughput
+  // instantiation: 1024 x 32 -3.3 %, 4096 x 2 -4.9 %, 2048 x 8 -4.4 %, 1024 x 256 -0.9 %, 4096 x 8 -0.35 %,
+  // 8192 x 8 +0.3 % (profiles/r02_chain_pause_sweep.txt).  On in both.
+  constexpr bool DIRECT_DIAG = true;
+  constexpr bool EARLY_HALF = true;
 
   if (tid == 0) {
     tma_prefetch_desc(&tmap);
@@ -1316,8 +1321,8 @@ k_chol_tasks(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ C
         pre1 = (int)stage;
         wait_full(stage, phase);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        if constexpr (MINB == 1 && CW == 4) {
-          // Chain-bound instantiation: this update sits on the dependency chain, and it is a SYRK --
+        if constexpr (CW == 4) {
+          // This update sits on the dependency chain, and it is a SYRK --
           // only fragments on or below the diagonal of the block are ever read (diag_factor works on
           // rows >= columns; what Cs holds above the diagonal never reaches a result).  Warp 2, whose
           // sub-tile lies strictly above the diagonal, takes tile columns 16..31 of warp 1's full

@@ -1532,11 +1532,13 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     // Two co-resident CTAs per SM keep the DMMA pipe fed in throughput mode; launches with few tasks
     // per SM are bound by the dependency chain diag(j) -> (j+1, j) -> diag(j+1) instead, and a CTA
     // that has its SM (and an uncapped register budget) to itself factors and solves faster (n=4096,
-    // one proposal: 1.36 ms vs 1.94 ms).  Measured crossover (tools/ctas_sweep.py, n = 300 .. 8192):
-    // about 24 tasks per SM.  GPB_CTAS_PER_SM_RT overrides (tuning).
+    // one proposal: 1.20 ms vs 1.47 ms).  GPB_CTAS_PER_SM_RT overrides (tuning).
     static int env_ctas = -1;
     if (env_ctas < 0) { const char* e = getenv("GPB_CTAS_PER_SM_RT"); env_ctas = e ? atoi(e) : 0; }
-    int ctas = (total >= 24LL * num_sms) ? CTAS_PER_SM : 1;
+    // crossover re-measured with the final kernels (profiles/r02_chain_pause_sweep.txt): ~18 tasks per SM from 16 block
+    // columns on, earlier for shorter chains (n = 300: ~9, n = 640: ~13)
+    const long long thr = g.nt >= 16 ? 18 : (6 + (3 * g.nt) / 4 < 8 ? 8 : 6 + (3 * g.nt) / 4);
+    int ctas = (total >= thr * num_sms) ? CTAS_PER_SM : 1;
     if (env_ctas > 0 && env_ctas <= CTAS_PER_SM) ctas = env_ctas;
     // GPB_GRID_CAP=k (tuning): at most k CTAs per SM in the grid while keeping the instantiation `ctas` selects
     static int env_cap = -1;
@@ -1551,7 +1553,7 @@ int launch_chol(cudaStream_t st, const Geom& g_in, double* mats, double* linvt, 
     // +3.5 %, x 256 +4.3 %) or the chain is short (n=300 x 256 +10 %).  GPB_CHAIN_PAUSE=0|1 overrides.
     static int env_pause = -2;
     if (env_pause == -2) { const char* e = getenv("GPB_CHAIN_PAUSE"); env_pause = e ? atoi(e) : -1; }
-    int pause = (ctas == 2 && !solve_only && g.nt >= 16 && total < (long long)PAUSE_TASKS_PER_SM * num_sms) ? 1 : 0;
+    int pause = (ctas == 2 && !solve_only && g.nt >= 32 && total < (long long)PAUSE_TASKS_PER_SM * num_sms) ? 1 : 0;
     if (chain_pause >= 0) pause = chain_pause;
     if (env_pause >= 0) pause = env_pause;
     if (ctas != 2 || num_sms > SCHED_MAXSM) pause = 0;

@@ -165,6 +165,10 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
     if (mode == 2 && ctj * TILE + TILE <= g.n &&
         (cti * TILE + TILE <= g.n || (cti * TILE >= g.npad && cti * TILE + TILE <= g.npad + g.m))) {
       const int c0 = tid >> 6;
+      const int nterms_reg = h.nterms;
+      const int tk0 = h.kind[0], tk1 = h.kind[1], tk2 = h.kind[2];
+      const double tp0 = h.p0[0], tp1 = h.p0[1], tp2 = h.p0[2];
+      const double tn0 = ninv2[0], tn1 = ninv2[1], tn2 = ninv2[2];
       const size_t step = (size_t)4 * g.ld;                       // this thread's columns are c0 + 4 e, e = 0..15
       double* pc = M + (size_t)(ctj * TILE + c0) * g.ld + R;
       // the nugget lands on this thread's entry e = (rl - c0) / 4 of a diagonal tile, if that is an integer
@@ -186,11 +190,9 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
           // d2 >= 0 (or NaN): it is zero iff all its bits are (a NaN never equals zero either way)
           nz = min(nz, (unsigned)__double2hiint(d2[u]) | (unsigned)__double2loint(d2[u]));
         }
-#pragma unroll 1
-        for (int t = 0; t < h.nterms; ++t) {
-          const double p0 = h.p0[t];
-          if (h.kind[t] == GPB_KIND_SE) {
-            const double ni = ninv2[t];
+        // one term: the same operations in the same order whichever way the terms are walked (left fold)
+        auto add_term = [&](int kind, double p0, double ni) {
+          if (kind == GPB_KIND_SE) {
             double xa[4], ea[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) xa[u] = __dmul_rn(d2[u], ni);
@@ -202,6 +204,15 @@ k_build(Geom g, const double* __restrict__ x, const double* __restrict__ y,
 #pragma unroll
             for (int u = 0; u < 4; ++u) s[u] = __dadd_rn(s[u], (d2[u] == 0.0) ? p0 : 0.0);
           }
+        };
+        if (nterms_reg <= 3) {
+          // the usual kernels (SE + white, SE + SE + white): parameters in registers, no loop over shared memory
+          add_term(tk0, tp0, tn0);
+          if (nterms_reg > 1) add_term(tk1, tp1, tn1);
+          if (nterms_reg > 2) add_term(tk2, tp2, tn2);
+        } else {
+#pragma unroll 1
+          for (int t = 0; t < h.nterms; ++t) add_term(h.kind[t], h.p0[t], ninv2[t]);
         }
         if ((ediag >> 2) == q) {
 #pragma unroll

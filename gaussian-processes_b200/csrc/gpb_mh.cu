@@ -263,6 +263,7 @@ k_mh_step(MhDev md, MhState s, Geom g, int it, int propose_next, const double* _
   const int c = blockIdx.x, tid = threadIdx.x;
   const double* M = mats + (size_t)c * g.mat_stride;
   double q = 0.0, u1 = 0.0, sl = 0.0;
+#pragma unroll 4   // the loads of four rounds in flight (same sums in the same order)
   for (int col = tid; col < g.n; col += blockDim.x) {
     const double u = M[(size_t)col * g.ld + g.rhs_row];
     const double l = M[(size_t)col * g.ld + col];
